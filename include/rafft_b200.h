@@ -1,0 +1,143 @@
+/*
+ * rafft_b200 -- C-ABI of the B200-native RAFFT folding hot path.
+ *
+ * The reference (lemerleau/RAFFT) has no plugin/FFI registry for this path: its boundary is
+ * the Python call  rafft.rafft.fold(sequence, nb_mode, max_stack, max_branch, min_hp,
+ * min_nrj, traj, temp, gc_wei, au_wei, gu_wei)   (reference rafft/rafft.py:219-239), and
+ * the only C-ABI it crosses is ViennaRNA's energy evaluation
+ *     vrna_fold_compound(seq, md, VRNA_OPTION_EVAL_ONLY) / vrna_eval_structure_pt(fc, pt)
+ * (reference rafft-rs/src/vienna.rs:20-24,31-34; Python: rafft/utils.py:18-21,135-138).
+ * The entry points below are what a binding for the path binds instead; each cites the
+ * reference interface it replaces.  Plain pointers and sizes only, integer status codes,
+ * no exceptions cross the ABI.  One context per CUDA device; a context is not thread-safe
+ * (mirrors `#[pyclass(unsendable)]`, reference rafft-rs/src/bindings.rs:10-11).
+ */
+#ifndef RAFFT_B200_H
+#define RAFFT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RAFFT_OK 0
+#define RAFFT_ERR_ARG 1      /* bad argument (NULL, n < 0, unsupported parameter value) */
+#define RAFFT_ERR_SEQ 2      /* letter outside A,C,G,U (reference: KeyError, rafft/utils.py:73-80) */
+#define RAFFT_ERR_CUDA 3     /* CUDA runtime failure; message in rafft_last_error */
+#define RAFFT_ERR_CAPACITY 4 /* a per-sequence device arena overflowed even after regrowth */
+
+/* Turner-2004 style nearest-neighbour parameters in dcal/mol.  Pair types 0..5 = CG GC GU
+ * UG AU UA, bases 0..3 = A C G U.  Replaces ViennaRNA's vrna_param_t as read by
+ * vrna_params_load (reference rafft-rs/src/vienna.rs:75-81). */
+#define RAFFT_MAX_SPECIAL 64
+typedef struct rafft_energy_params {
+  int32_t stack[6][6];
+  int32_t hairpin[31], bulge[31], interior[31];
+  int32_t mismatchH[6][4][4], mismatchI[6][4][4], mismatch1nI[6][4][4];
+  int32_t mismatch23I[6][4][4], mismatchM[6][4][4], mismatchExt[6][4][4];
+  int32_t dangle5[6][4], dangle3[6][4];
+  int32_t int11[6][6][4][4];
+  int32_t int21[6][6][4][4][4];
+  int32_t int22[6][6][4][4][4][4];
+  int32_t ninio, max_ninio, ml_base, ml_intern, ml_closing, terminal_au;
+  double lxc;
+  int32_t n_tri, n_tetra, n_hexa;
+  char tri[RAFFT_MAX_SPECIAL][8];    /* 5 letters, NUL padded */
+  char tetra[RAFFT_MAX_SPECIAL][8];  /* 6 letters */
+  char hexa[RAFFT_MAX_SPECIAL][12];  /* 8 letters */
+  int32_t tri_e[RAFFT_MAX_SPECIAL], tetra_e[RAFFT_MAX_SPECIAL], hexa_e[RAFFT_MAX_SPECIAL];
+} rafft_energy_params;
+
+/* Arguments of fold() (reference rafft/rafft.py:219-221; CLI flags bin/rafft:11-27). */
+typedef struct rafft_params {
+  int32_t nb_mode;    /* -n   number of positional lags searched per unpaired region */
+  int32_t max_stack;  /* -ms  structures saved per folding step */
+  int32_t max_branch; /* --max_branch (fold() default 100, CLI default 1000) */
+  int32_t min_hp;     /* -mh  minimum unpaired positions in a hairpin */
+  int32_t traj;       /* --traj: 1 = return every step, 0 = only the last one */
+  double min_nrj;     /* -mn  a stem is kept iff its energy change is < min_nrj (kcal/mol) */
+  double temp;        /* --temp: only 37.0 is supported by the built-in tables */
+  double gc_wei, au_wei, gu_wei; /* -gc -au -gu pair weights of the correlation */
+} rafft_params;
+
+/* Work counters per sequence (the ALGORITHMIC work of the reference's formulation, used for
+ * the roofline figures; definitions in DESIGN.md section 6). */
+enum {
+  RAFFT_CNT_STEPS = 0,    /* bfs_pairs calls (rafft/rafft.py:156) */
+  RAFFT_CNT_NODE_EXP,     /* create_childs calls the reference makes (rafft/rafft.py:168) */
+  RAFFT_CNT_W_CORR,       /* sum over those calls of Lv(Lv+1)/2 pair-weight accumulations */
+  RAFFT_CNT_W_SCAN,       /* sum over (call, ranked lag) of ceil(d/2) scan positions */
+  RAFFT_CNT_N_EVAL,       /* eval_one_struct calls (rafft/rafft.py:98,192) */
+  RAFFT_CNT_UNIQ_NODES,   /* unique loop regions this implementation actually expanded */
+  RAFFT_CNT_UNIQ_W_CORR,  /* pair-weight accumulations actually performed */
+  RAFFT_CNT_UNIQ_W_SCAN,  /* scan positions actually visited */
+  RAFFT_CNT_COMBOS,       /* stem combinations enumerated (itertools.product items) */
+  RAFFT_CNT_N
+};
+
+/* Result of one rafft_fold_batch call; all arrays are host memory owned by the library
+ * until rafft_result_free.  Sequence i has the unique structures
+ * [struct_off[i], struct_off[i+1]); structure s of sequence i (length L) has energy
+ * energy_dcal[s] (integer dcal/mol; the reference's float is float32(E/100)) and
+ * dot-bracket text db[db_off[i] + (s - struct_off[i]) * L .. + L) (not NUL terminated).
+ * Its folding steps are [step_off[i], step_off[i+1]); step t lists the structures of its
+ * beam in order as entry_struct[entry_off[t] .. entry_off[t+1]) (indices local to the
+ * sequence).  With traj = 0 only the final beam is returned (one step per sequence). */
+typedef struct rafft_result {
+  int32_t n_seq;
+  const int32_t *status;        /* n_seq: RAFFT_OK or an error code for that sequence */
+  const int64_t *struct_off;    /* n_seq + 1 */
+  const int32_t *energy_dcal;   /* struct_off[n_seq] */
+  const int64_t *db_off;        /* n_seq + 1 */
+  const char *db;               /* db_off[n_seq] */
+  const int64_t *step_off;      /* n_seq + 1 */
+  const int64_t *entry_off;     /* step_off[n_seq] + 1 */
+  const int32_t *entry_struct;  /* entry_off[step_off[n_seq]] */
+  const int64_t *counters;      /* n_seq * RAFFT_CNT_N */
+  double kernel_ms;             /* device time of the fold kernel(s), CUDA events */
+  int64_t kernel_launches;      /* number of kernel launches this call made */
+  int64_t h2d_bytes, d2h_bytes; /* bytes copied host->device / device->host by this call */
+} rafft_result;
+
+typedef struct rafft_ctx rafft_ctx;
+
+/* Fill *ep with the built-in Turner-2004 tables (reconstructed). */
+void rafft_default_energy_params(rafft_energy_params *ep);
+
+/* Create a context on a CUDA device.  ep == NULL selects the built-in tables.  Replaces
+ * RNA.md()/RNA.fold_compound(...) (reference rafft/utils.py:18-21) and
+ * vrna_fold_compound (rafft-rs/src/vienna.rs:20-24).  Fails (RAFFT_ERR_CUDA) when no
+ * usable CUDA device exists -- there is no CPU fallback. */
+int rafft_create(rafft_ctx **out, int cuda_device, const rafft_energy_params *ep);
+void rafft_destroy(rafft_ctx *ctx);
+/* Message of the last failing call on ctx (ctx == NULL: last rafft_create failure). */
+const char *rafft_last_error(const rafft_ctx *ctx);
+
+/* Fold n sequences (ASCII, concatenated in seqs; sequence i = seqs[offs[i] .. offs[i+1])).
+ * Replaces n calls of rafft.rafft.fold (reference rafft/rafft.py:219-239).  Synchronous. */
+int rafft_fold_batch(rafft_ctx *ctx, const char *seqs, const int64_t *offs, int32_t n,
+                     const rafft_params *params, rafft_result **out);
+void rafft_result_free(rafft_result *res);
+
+/* Same, but the inputs already live in device memory (d_seqs: the concatenated letters,
+ * d_offs: n+1 int64) and the timed work is the kernel only; results are still returned on
+ * the host.  Used by bench.py for the device-resident figure. */
+int rafft_fold_batch_device(rafft_ctx *ctx, const void *d_seqs, const void *d_offs, int32_t n,
+                            int64_t total_len, int32_t max_len, const rafft_params *params,
+                            rafft_result **out);
+
+/* Free energy of whole structures (dot-bracket, same layout as seqs) in dcal/mol, on the
+ * device, one structure per sequence.  Replaces vrna_eval_structure_pt
+ * (reference rafft-rs/src/vienna.rs:31-34) / fold_compound.eval_structure
+ * (rafft/utils.py:135-138). */
+int rafft_eval_structures(rafft_ctx *ctx, const char *seqs, const char *structs,
+                          const int64_t *offs, int32_t n, int32_t *energy_dcal);
+
+/* Library/build identification, e.g. "rafft_b200 0.1 sm_100a". */
+const char *rafft_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAFFT_B200_H */
