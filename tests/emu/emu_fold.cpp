@@ -1,0 +1,84 @@
+/*
+ * TEST-ONLY host emulation of the device code: compiles rafft_b200/csrc/fold_core.cuh with a
+ * host execution policy (every `par` phase runs its iterations one after the other, forward
+ * or reversed) so that the ordering logic of the CUDA path can be checked against the
+ * oracle in the CPU test tier.  This is NOT a CPU fallback: nothing in rafft_b200/ loads
+ * it and the product fails loudly without the CUDA library.
+ */
+#include <stdio.h>
+#include <stdlib.h>
+#include <string>
+#include <vector>
+#include "../../rafft_b200/csrc/host_common.h"
+
+using namespace rafft;
+
+extern "C" {
+
+void emu_default_energy_params(rafft_energy_params *ep) { default_energy_params(ep); }
+
+/* Same text format as oracle_fold.  hiwater: 8 ints (nodes, pool16, cands, store, nlist,
+ * seen, steps, arena KiB).  Returns the sequence status or a negative argument error. */
+int emu_fold(const rafft_energy_params *ep_in, const char *seq, int L, const rafft_params *prm,
+             int reverse, int nthreads, int scale, char **text, int64_t *cnt, int32_t *hiwater) {
+  rafft_energy_params *ep = (rafft_energy_params *)malloc(sizeof *ep);
+  if (ep_in) *ep = *ep_in; else default_energy_params(ep);
+  DevEnergy *D = (DevEnergy *)malloc(sizeof *D);
+  FoldParams F;
+  std::string err;
+  if (!build_dev_energy(ep, D, err) || !build_fold_params(prm, &F, err)) {
+    fprintf(stderr, "emu_fold: %s\n", err.c_str());
+    free(ep); free(D);
+    return -1;
+  }
+  Exec::order() = reverse;
+  Exec::emu_threads() = nthreads > 0 ? nthreads : 32;
+  Caps caps = make_caps(L, F, Exec::nthreads(), scale > 0 ? scale : 1);
+  std::vector<char> arena((size_t)caps.arena_bytes);
+  Fold f;
+  f.E = D; f.prm = F; f.caps = caps;
+  arena_carve(f.A, arena.data(), caps, F, Exec::nthreads());
+  BlockShared sh;
+  f.sh = &sh;
+  /* output for one sequence */
+  int64_t scap = (int64_t)caps.store_cap, ecap = (int64_t)caps.step_cap * F.max_stack;
+  std::vector<int32_t> status(1), nstruct(1), nstep(1), energy(scap), step_n(caps.step_cap), entries(ecap);
+  std::vector<int64_t> sstruct(1), sdb(1), sstep(1), sentry(1), counters(CNT_N);
+  std::vector<char> db((size_t)scap * (L > 0 ? L : 1));
+  unsigned long long cursors[8] = {0};
+  OutBuf out;
+  out.status = status.data(); out.seq_struct = sstruct.data(); out.seq_nstruct = nstruct.data();
+  out.seq_db = sdb.data(); out.seq_step = sstep.data(); out.seq_nstep = nstep.data();
+  out.seq_entry = sentry.data(); out.counters = counters.data(); out.energy = energy.data();
+  out.db = db.data(); out.step_n = step_n.data(); out.entries = entries.data(); out.cursors = cursors;
+  out.struct_cap = scap; out.db_cap = (int64_t)db.size(); out.step_cap = caps.step_cap; out.entry_cap = ecap;
+  f.run(seq, L, 0, out);
+  if (cnt) for (int k = 0; k < CNT_N; k++) cnt[k] = counters[k];
+  if (hiwater) {
+    hiwater[0] = sh.n_node; hiwater[1] = sh.n_pool16; hiwater[2] = sh.n_cand; hiwater[3] = sh.n_store;
+    hiwater[4] = sh.n_nlist; hiwater[5] = sh.n_seen; hiwater[6] = sh.n_steps;
+    hiwater[7] = (int32_t)(caps.arena_bytes >> 10);
+  }
+  if (text) {
+    std::string o;
+    char buf[64];
+    int64_t e = sentry[0];
+    for (int s = 0; s < nstep[0]; s++) {
+      snprintf(buf, sizeof buf, "# %d\n", s);
+      o += buf;
+      for (int b = 0; b < step_n[sstep[0] + s]; b++, e++) {
+        int k = entries[e];
+        o.append(db.data() + sdb[0] + (size_t)k * L, L);
+        snprintf(buf, sizeof buf, " %d\n", energy[sstruct[0] + k]);
+        o += buf;
+      }
+    }
+    *text = (char *)malloc(o.size() + 1);
+    memcpy(*text, o.c_str(), o.size() + 1);
+  }
+  free(ep); free(D);
+  return status[0];
+}
+
+void emu_free(void *p) { free(p); }
+}
