@@ -725,7 +725,8 @@ struct Fold {
       sh->n_seen = 0; sh->n_todo = 0; sh->n_expand = 0; sh->beam_n = 0; sh->n_new = 0;
       sh->nb_branch = 0; sh->n_steps = 0; sh->n_traj = 0;
       for (int k = 0; k < CNT_N; k++) sh->cnt[k] = 0;
-      if (L > caps.L_max || L < 1) sh->status = ST_ERR_CAPACITY;
+      if (L > caps.L_max) sh->status = ST_ERR_CAPACITY;
+      else if (L < 1) sh->status = ST_ERR_SEQ; /* the reference cannot fold an empty sequence */
     RF_SINGLE_END
     if (sh->status == ST_OK) {
       RF_PAR_BEGIN(i, L)

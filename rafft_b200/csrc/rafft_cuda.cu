@@ -1,0 +1,660 @@
+/*
+ * rafft_cuda.cu -- the C-ABI library (include/rafft_b200.h) over the sm_100a kernels.
+ *
+ * Kernels in this file:
+ *   order_kernel   longest-first processing order of the batch (rank by counting)
+ *   fold_kernel    persistent thread blocks; each block pulls the next sequence from a device
+ *                  queue and runs the whole fold (fold_core.cuh) out of its own arena
+ *   scan_kernel    exclusive scans that turn per-sequence counts into the ordered layout
+ *   pack_kernel    gathers the bump-allocated results into input order
+ *   eval_kernel    whole-structure loop-decomposition energies (rafft_eval_structures)
+ *
+ * There is no CPU fallback: every entry point fails with RAFFT_ERR_CUDA when no device is
+ * usable.  Nothing here includes or links anything under oracle/.
+ */
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <algorithm>
+#include <string>
+#include <vector>
+#include "host_common.h"
+
+using namespace rafft;
+
+#define RF_BLOCK_THREADS_MAX 256
+
+/* ------------------------------------------------------------------------------------ */
+/* kernels                                                                               */
+
+/* order[r] = index of the sequence with the r-th largest length (ties: lower index first);
+ * subset == nullptr: all n sequences, else the n listed ones. */
+__global__ void order_kernel(const int64_t *__restrict__ offs, const int32_t *__restrict__ subset,
+                             int n, int32_t *__restrict__ order) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int si = subset ? subset[i] : i;
+  int64_t li = offs[si + 1] - offs[si];
+  int r = 0;
+  for (int k = 0; k < n; k++) {
+    int sk = subset ? subset[k] : k;
+    int64_t lk = offs[sk + 1] - offs[sk];
+    r += (lk > li) || (lk == li && k < i);
+  }
+  order[r] = si;
+}
+
+__global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX)
+fold_kernel(const DevEnergy *__restrict__ E, FoldParams prm, Caps caps, char *arenas,
+            const char *__restrict__ seqs, const int64_t *__restrict__ offs,
+            const int32_t *__restrict__ order, int n, OutBuf out) {
+  __shared__ Fold f;
+  __shared__ BlockShared sh;
+  __shared__ int next;
+  if (threadIdx.x == 0) {
+    f.E = E; f.prm = prm; f.caps = caps; f.sh = &sh;
+    arena_carve(f.A, arenas + (size_t)blockIdx.x * (size_t)caps.arena_bytes, caps, prm, blockDim.x);
+  }
+  for (;;) {
+    __syncthreads();
+    if (threadIdx.x == 0) next = (int)atomicAdd(&out.cursors[4], 1ULL);
+    __syncthreads();
+    const int q = next;
+    if (q >= n) break;
+    const int si = order[q];
+    const int64_t o = offs[si];
+    f.run(seqs + o, (int)(offs[si + 1] - o), si, out);
+  }
+}
+
+/* One block.  Ordered offsets: struct_off/db_off/step_off (n+1 each) and the per-sequence
+ * base of its entries, ent_base (n+1); totals[0..3] = structures, db bytes, steps, entries. */
+__global__ void scan_kernel(const int64_t *__restrict__ offs, int n, OutBuf out,
+                            int64_t *__restrict__ struct_off, int64_t *__restrict__ db_off,
+                            int64_t *__restrict__ step_off, int64_t *__restrict__ ent_base,
+                            int64_t *__restrict__ totals) {
+  __shared__ long long part[4][1024];
+  const int T = blockDim.x, t = threadIdx.x;
+  const int per = (n + T - 1) / T;
+  const int lo = min(n, t * per), hi = min(n, lo + per);
+  long long a[4] = {0, 0, 0, 0};
+  for (int i = lo; i < hi; i++) {
+    long long ns = out.seq_nstruct[i], L = offs[i + 1] - offs[i];
+    long long ne = 0;
+    for (int s = 0; s < out.seq_nstep[i]; s++) ne += out.step_n[out.seq_step[i] + s];
+    a[0] += ns; a[1] += ns * L; a[2] += out.seq_nstep[i]; a[3] += ne;
+  }
+  for (int k = 0; k < 4; k++) part[k][t] = a[k];
+  __syncthreads();
+  if (t == 0) {
+    for (int k = 0; k < 4; k++) {
+      long long run = 0;
+      for (int j = 0; j < T; j++) { long long v = part[k][j]; part[k][j] = run; run += v; }
+      totals[k] = run;
+    }
+  }
+  __syncthreads();
+  for (int k = 0; k < 4; k++) a[k] = part[k][t];
+  for (int i = lo; i < hi; i++) {
+    long long ns = out.seq_nstruct[i], L = offs[i + 1] - offs[i];
+    long long ne = 0;
+    for (int s = 0; s < out.seq_nstep[i]; s++) ne += out.step_n[out.seq_step[i] + s];
+    struct_off[i] = a[0]; db_off[i] = a[1]; step_off[i] = a[2]; ent_base[i] = a[3];
+    a[0] += ns; a[1] += ns * L; a[2] += out.seq_nstep[i]; a[3] += ne;
+  }
+  /* every thread whose range ends at n holds the totals (empty trailing ranges included) */
+  if (hi == n) { struct_off[n] = a[0]; db_off[n] = a[1]; step_off[n] = a[2]; ent_base[n] = a[3]; }
+}
+
+/* One block per sequence: copy its structures, dot-brackets, steps and entries into the
+ * ordered layout.  entry_off has step_off[n] + 1 elements. */
+__global__ void pack_kernel(const int64_t *__restrict__ offs, int n, OutBuf out,
+                            const int64_t *__restrict__ struct_off, const int64_t *__restrict__ db_off,
+                            const int64_t *__restrict__ step_off, const int64_t *__restrict__ ent_base,
+                            int32_t *__restrict__ energy, char *__restrict__ db,
+                            int64_t *__restrict__ entry_off, int32_t *__restrict__ entry_struct) {
+  const int i = blockIdx.x;
+  const int ns = out.seq_nstruct[i], nt = out.seq_nstep[i];
+  const int64_t L = offs[i + 1] - offs[i];
+  const int64_t s_src = out.seq_struct[i], d_src = out.seq_db[i], t_src = out.seq_step[i],
+                e_src = out.seq_entry[i];
+  const int64_t s_dst = struct_off[i], d_dst = db_off[i], t_dst = step_off[i], e_dst = ent_base[i];
+  for (int k = threadIdx.x; k < ns; k += blockDim.x) energy[s_dst + k] = out.energy[s_src + k];
+  const int64_t nbytes = (int64_t)ns * L;
+  for (int64_t k = threadIdx.x; k < nbytes; k += blockDim.x) db[d_dst + k] = out.db[d_src + k];
+  const int64_t ne = ent_base[i + 1] - e_dst;
+  for (int64_t k = threadIdx.x; k < ne; k += blockDim.x) entry_struct[e_dst + k] = out.entries[e_src + k];
+  if (threadIdx.x == 0) {
+    int64_t run = e_dst;
+    for (int s = 0; s < nt; s++) { entry_off[t_dst + s] = run; run += out.step_n[t_src + s]; }
+    if (i == n - 1) entry_off[t_dst + nt] = run;
+  }
+}
+
+/* Whole-structure energy: one warp per structure.  Lane 0 builds the pair table with an
+ * explicit stack, then the lanes share the loops (one loop per closing pair + exterior). */
+__global__ void eval_kernel(const DevEnergy *__restrict__ E, const char *__restrict__ seqs,
+                            const char *__restrict__ dbs, const int64_t *__restrict__ offs, int n,
+                            int32_t *__restrict__ scratch /* 2 ints per letter */,
+                            uint8_t *__restrict__ codes, int32_t *__restrict__ energy) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= n) return;
+  const int64_t o = offs[warp];
+  const int L = (int)(offs[warp + 1] - o);
+  const char *seq = seqs + o, *db = dbs + o;
+  int32_t *pt = scratch + 2 * o, *st = pt + L;
+  uint8_t *code = codes + o;
+  int bad = 0;
+  for (int k = lane; k < L; k += 32) {
+    char ch = seq[k];
+    int c = ch == 'A' ? 0 : ch == 'C' ? 1 : ch == 'G' ? 2 : ch == 'U' ? 3 : -1;
+    if (c < 0) { bad = 1; c = 0; }
+    code[k] = (uint8_t)c;
+  }
+  bad = __any_sync(0xffffffffu, bad);
+  __syncwarp();
+  int ok = 1;
+  if (lane == 0) {
+    int sp = 0;
+    for (int k = 0; k < L && ok; k++) {
+      pt[k] = -1;
+      if (db[k] == '(') st[sp++] = k;
+      else if (db[k] == ')') {
+        if (!sp) ok = 0;
+        else { int i = st[--sp]; pt[i] = k; pt[k] = i; }
+      } else if (db[k] != '.') ok = 0;
+    }
+    if (sp) ok = 0;
+  }
+  ok = __shfl_sync(0xffffffffu, ok, 0);
+  __syncwarp();
+  if (!ok || bad) { if (lane == 0) energy[warp] = INT32_MIN; return; }
+  EnergyView ev; ev.P = E; ev.s = code; ev.L = L;
+  long long e = 0;
+  int nc = 0;
+  for (int i = lane - 1; i < L; i += 32) { /* i = -1: exterior loop */
+    int j;
+    if (i >= 0) { j = pt[i]; if (j <= i) continue; if (pair_type(code[i], code[j]) < 0) { nc = 1; continue; } }
+    else j = L;
+    int nbr = 0, p1 = -1, q1 = -1, unp = 0;
+    for (int p = i + 1; p < j;) {
+      if (pt[p] > p) { if (!nbr) { p1 = p; q1 = pt[p]; } nbr++; p = pt[p] + 1; }
+      else { unp++; p++; }
+    }
+    if (i < 0) {
+      for (int p = 0; p < L;) {
+        if (pt[p] > p) { if (pair_type(code[p], code[pt[p]]) >= 0) e += e_extstem(ev, p, pt[p]); p = pt[p] + 1; }
+        else p++;
+      }
+    } else if (nbr == 0) e += e_hairpin(ev, i, j);
+    else if (nbr == 1) { if (pair_type(code[p1], code[q1]) >= 0) e += e_interior(ev, i, j, p1, q1); }
+    else {
+      int tt = pair_type(code[j], code[i]);
+      e += E->ml_closing + (long long)E->ml_base * unp + E->ml_intern +
+           E->mmM[tt * 16 + code[j - 1] * 4 + code[i + 1]] + (tt > 1 ? E->terminal_au : 0);
+      for (int p = i + 1; p < j;) {
+        if (pt[p] > p) { if (pair_type(code[p], code[pt[p]]) >= 0) e += e_mlstem(ev, p, pt[p]); p = pt[p] + 1; }
+        else p++;
+      }
+    }
+  }
+  for (int d = 16; d; d >>= 1) {
+    e += __shfl_xor_sync(0xffffffffu, e, d);
+    nc |= __shfl_xor_sync(0xffffffffu, nc, d);
+  }
+  if (lane == 0) energy[warp] = nc ? INT32_MIN : (e > 2000000000LL ? 2000000000 : (int32_t)e);
+}
+
+/* ------------------------------------------------------------------------------------ */
+/* host side                                                                             */
+
+struct DevBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+};
+
+struct HostBlock {  /* pinned host memory handed out inside a rafft_result */
+  void *p = nullptr;
+  size_t cap = 0;
+};
+
+struct rafft_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  DevEnergy *d_energy = nullptr;
+  DevBuf arenas, seqs, offs, order, subset, idx, big, ordered, scan, evalbuf;
+  std::vector<HostBlock> pinned_free;
+  int64_t *h_small = nullptr; /* pinned: totals + cursors */
+  int block_threads = 128;
+  int blocks_per_sm = 8;
+  std::string err;
+};
+
+struct ResultImpl {
+  rafft_result pub;
+  rafft_ctx *ctx;
+  HostBlock block;
+};
+
+static std::string g_create_err;
+
+#define CK(call)                                                                       \
+  do {                                                                                 \
+    cudaError_t e_ = (call);                                                           \
+    if (e_ != cudaSuccess) {                                                           \
+      ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);                   \
+      return RAFFT_ERR_CUDA;                                                           \
+    }                                                                                  \
+  } while (0)
+
+static int dev_reserve(rafft_ctx *ctx, DevBuf &b, size_t bytes) {
+  if (bytes <= b.cap) return RAFFT_OK;
+  if (b.p) { CK(cudaFree(b.p)); b.p = nullptr; b.cap = 0; }
+  size_t want = bytes + bytes / 8 + 256;
+  cudaError_t e = cudaMalloc(&b.p, want);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    want = bytes;
+    e = cudaMalloc(&b.p, want);
+  }
+  if (e != cudaSuccess) {
+    b.p = nullptr;
+    ctx->err = std::string("cudaMalloc(") + std::to_string(bytes) + "): " + cudaGetErrorString(e);
+    return RAFFT_ERR_CUDA;
+  }
+  b.cap = want;
+  return RAFFT_OK;
+}
+
+static int host_block_get(rafft_ctx *ctx, size_t bytes, HostBlock *hb) {
+  int best = -1;
+  for (size_t k = 0; k < ctx->pinned_free.size(); k++)
+    if (ctx->pinned_free[k].cap >= bytes && (best < 0 || ctx->pinned_free[k].cap < ctx->pinned_free[best].cap))
+      best = (int)k;
+  if (best >= 0) {
+    *hb = ctx->pinned_free[best];
+    ctx->pinned_free.erase(ctx->pinned_free.begin() + best);
+    return RAFFT_OK;
+  }
+  /* drop smaller cached blocks before allocating a larger one */
+  for (auto &b : ctx->pinned_free) cudaFreeHost(b.p);
+  ctx->pinned_free.clear();
+  size_t want = bytes + bytes / 4 + 4096;
+  CK(cudaHostAlloc(&hb->p, want, cudaHostAllocDefault));
+  hb->cap = want;
+  return RAFFT_OK;
+}
+
+extern "C" {
+
+const char *rafft_version(void) { return "rafft_b200 0.1 sm_100a"; }
+
+void rafft_default_energy_params(rafft_energy_params *ep) {
+  if (ep) default_energy_params(ep);
+}
+
+const char *rafft_last_error(const rafft_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+void rafft_destroy(rafft_ctx *ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  DevBuf *bufs[] = {&ctx->arenas, &ctx->seqs, &ctx->offs, &ctx->order, &ctx->subset, &ctx->idx,
+                    &ctx->big, &ctx->ordered, &ctx->scan, &ctx->evalbuf};
+  for (DevBuf *b : bufs)
+    if (b->p) cudaFree(b->p);
+  for (auto &b : ctx->pinned_free) cudaFreeHost(b.p);
+  if (ctx->h_small) cudaFreeHost(ctx->h_small);
+  if (ctx->d_energy) cudaFree(ctx->d_energy);
+  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+int rafft_create(rafft_ctx **out, int cuda_device, const rafft_energy_params *ep_in) {
+  if (!out) { g_create_err = "rafft_create: out is NULL"; return RAFFT_ERR_ARG; }
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    g_create_err = std::string("rafft_create: no usable CUDA device (") +
+                   (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0") +
+                   "); this library has no CPU fallback";
+    (void)cudaGetLastError();
+    return RAFFT_ERR_CUDA;
+  }
+  if (cuda_device < 0 || cuda_device >= ndev) {
+    g_create_err = "rafft_create: cuda_device out of range";
+    return RAFFT_ERR_ARG;
+  }
+  rafft_energy_params *ep = (rafft_energy_params *)malloc(sizeof *ep);
+  if (ep_in) *ep = *ep_in; else default_energy_params(ep);
+  DevEnergy *D = (DevEnergy *)malloc(sizeof *D);
+  std::string err;
+  if (!build_dev_energy(ep, D, err)) {
+    g_create_err = "rafft_create: " + err;
+    free(ep); free(D);
+    return RAFFT_ERR_ARG;
+  }
+  free(ep);
+  rafft_ctx *ctx = new rafft_ctx;
+  ctx->device = cuda_device;
+  int rc = [&]() -> int {
+    CK(cudaSetDevice(cuda_device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, cuda_device));
+    ctx->sm_count = prop.multiProcessorCount;
+    CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&ctx->ev0));
+    CK(cudaEventCreate(&ctx->ev1));
+    CK(cudaMalloc((void **)&ctx->d_energy, sizeof(DevEnergy)));
+    CK(cudaMemcpy(ctx->d_energy, D, sizeof(DevEnergy), cudaMemcpyHostToDevice));
+    CK(cudaHostAlloc((void **)&ctx->h_small, 64 * sizeof(int64_t), cudaHostAllocDefault));
+    const char *s = getenv("RAFFT_BLOCK_THREADS");
+    if (s) { int v = atoi(s); if (v >= 32 && v <= RF_BLOCK_THREADS_MAX && v % 32 == 0) ctx->block_threads = v; }
+    s = getenv("RAFFT_BLOCKS_PER_SM");
+    if (s) { int v = atoi(s); if (v >= 1 && v <= 32) ctx->blocks_per_sm = v; }
+    return RAFFT_OK;
+  }();
+  free(D);
+  if (rc != RAFFT_OK) {
+    g_create_err = "rafft_create: " + ctx->err;
+    rafft_destroy(ctx);
+    return rc;
+  }
+  *out = ctx;
+  return RAFFT_OK;
+}
+
+void rafft_result_free(rafft_result *res) {
+  if (!res) return;
+  ResultImpl *r = (ResultImpl *)res;
+  if (r->block.p) r->ctx->pinned_free.push_back(r->block);
+  delete r;
+}
+
+}  // extern "C"
+
+/* Layout of the index part of OutBuf inside ctx->idx for n sequences. */
+static size_t idx_layout(OutBuf &o, char *base, int n) {
+  size_t off = 0;
+  auto carve = [&](size_t bytes) { off = align_up(off, 16); char *p = base ? base + off : nullptr; off += bytes; return p; };
+  o.cursors = (unsigned long long *)carve(8 * sizeof(unsigned long long));
+  o.status = (int32_t *)carve(sizeof(int32_t) * (size_t)n);
+  o.seq_struct = (int64_t *)carve(sizeof(int64_t) * (size_t)n);
+  o.seq_nstruct = (int32_t *)carve(sizeof(int32_t) * (size_t)n);
+  o.seq_db = (int64_t *)carve(sizeof(int64_t) * (size_t)n);
+  o.seq_step = (int64_t *)carve(sizeof(int64_t) * (size_t)n);
+  o.seq_nstep = (int32_t *)carve(sizeof(int32_t) * (size_t)n);
+  o.seq_entry = (int64_t *)carve(sizeof(int64_t) * (size_t)n);
+  o.counters = (int64_t *)carve(sizeof(int64_t) * (size_t)n * CNT_N);
+  return align_up(off, 256);
+}
+
+static size_t big_layout(OutBuf &o, char *base) {
+  size_t off = 0;
+  auto carve = [&](size_t bytes) { off = align_up(off, 256); char *p = base ? base + off : nullptr; off += bytes; return p; };
+  o.energy = (int32_t *)carve(sizeof(int32_t) * (size_t)o.struct_cap);
+  o.db = (char *)carve((size_t)o.db_cap);
+  o.step_n = (int32_t *)carve(sizeof(int32_t) * (size_t)o.step_cap);
+  o.entries = (int32_t *)carve(sizeof(int32_t) * (size_t)o.entry_cap);
+  return align_up(off, 256);
+}
+
+/* The fold proper, inputs on the device.  h_offs: host copy of the offsets (n+1). */
+static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs, const int64_t *h_offs,
+                       int32_t n, const rafft_params *params, rafft_result **out_res,
+                       int64_t h2d_bytes) {
+  std::string err;
+  FoldParams F;
+  if (!build_fold_params(params, &F, err)) { ctx->err = "rafft_fold_batch: " + err; return RAFFT_ERR_ARG; }
+  int L_max = 1;
+  int64_t total_len = h_offs[n] - h_offs[0];
+  for (int i = 0; i < n; i++) {
+    int64_t L = h_offs[i + 1] - h_offs[i];
+    if (L < 0 || L > 4096) {
+      ctx->err = "rafft_fold_batch: sequence length must be in [0, 4096]";
+      return RAFFT_ERR_ARG;
+    }
+    if (L > L_max) L_max = (int)L;
+  }
+  const int T = ctx->block_threads;
+  ResultImpl *R = new ResultImpl;
+  memset(&R->pub, 0, sizeof R->pub);
+  R->ctx = ctx;
+  R->block = HostBlock();
+  auto fail = [&](int rc) { rafft_result_free(&R->pub); return rc; };
+  int64_t launches = 0, d2h = 0;
+  float kernel_ms = 0.f;
+
+  /* index part of the output */
+  OutBuf O;
+  memset(&O, 0, sizeof O);
+  size_t idx_bytes = idx_layout(O, nullptr, n);
+  if (int rc = dev_reserve(ctx, ctx->idx, idx_bytes)) return fail(rc);
+  idx_layout(O, (char *)ctx->idx.p, n);
+  if (cudaMemsetAsync(ctx->idx.p, 0, idx_bytes, ctx->stream) != cudaSuccess) { ctx->err = "memset"; return fail(RAFFT_ERR_CUDA); }
+  if (int rc = dev_reserve(ctx, ctx->order, sizeof(int32_t) * (size_t)(n + 1))) return fail(rc);
+  if (int rc = dev_reserve(ctx, ctx->subset, sizeof(int32_t) * (size_t)(n + 1))) return fail(rc);
+
+  std::vector<int32_t> todo;          /* sequences still to fold (empty = all) */
+  std::vector<int32_t> h_status(n > 0 ? n : 1);
+  int scale = 1;
+  int64_t used[4] = {0, 0, 0, 0};      /* cursors after the previous round */
+  for (int round = 0; n > 0; round++) {
+    const int m = round == 0 ? n : (int)todo.size();
+    int Lr = L_max;
+    if (round > 0) {
+      Lr = 1;
+      for (int i : todo) Lr = std::max<int64_t>(Lr, h_offs[i + 1] - h_offs[i]);
+    }
+    Caps caps = make_caps(Lr, F, T, scale);
+    /* output capacities for this round (bump-allocated after what is already used) */
+    int64_t per_struct = F.traj ? caps.store_cap : F.max_stack;
+    int64_t per_step = F.traj ? caps.step_cap : 1;
+    int64_t sum_L = 0;
+    if (round == 0) sum_L = total_len;
+    else for (int i : todo) sum_L += h_offs[i + 1] - h_offs[i];
+    OutBuf N = O;
+    N.struct_cap = used[0] + per_struct * m;
+    N.db_cap = used[1] + per_struct * sum_L;
+    N.step_cap = used[2] + per_step * m;
+    N.entry_cap = used[3] + (F.traj ? per_step * F.max_stack : (int64_t)F.max_stack) * m;
+    size_t big_bytes = big_layout(N, nullptr);
+    if (round == 0) {
+      if (int rc = dev_reserve(ctx, ctx->big, big_bytes)) return fail(rc);
+      big_layout(N, (char *)ctx->big.p);
+    } else {
+      DevBuf nb;
+      if (int rc = dev_reserve(ctx, nb, big_bytes)) return fail(rc);
+      big_layout(N, (char *)nb.p);
+      cudaMemcpyAsync(N.energy, O.energy, sizeof(int32_t) * (size_t)used[0], cudaMemcpyDeviceToDevice, ctx->stream);
+      cudaMemcpyAsync(N.db, O.db, (size_t)used[1], cudaMemcpyDeviceToDevice, ctx->stream);
+      cudaMemcpyAsync(N.step_n, O.step_n, sizeof(int32_t) * (size_t)used[2], cudaMemcpyDeviceToDevice, ctx->stream);
+      cudaMemcpyAsync(N.entries, O.entries, sizeof(int32_t) * (size_t)used[3], cudaMemcpyDeviceToDevice, ctx->stream);
+      CK(cudaStreamSynchronize(ctx->stream));
+      cudaFree(ctx->big.p);
+      ctx->big = nb;
+    }
+    O = N;
+    /* arenas: as many resident blocks as the launch can use, within the memory budget */
+    size_t free_b = 0, total_b = 0;
+    CK(cudaMemGetInfo(&free_b, &total_b));
+    int64_t grid = std::min<int64_t>(m, (int64_t)ctx->sm_count * ctx->blocks_per_sm);
+    int64_t budget = (int64_t)((free_b + ctx->arenas.cap) * 0.6);
+    if (grid * caps.arena_bytes > budget) grid = std::max<int64_t>(1, budget / caps.arena_bytes);
+    if (int rc = dev_reserve(ctx, ctx->arenas, (size_t)(grid * caps.arena_bytes))) return fail(rc);
+    /* queue */
+    const int32_t *d_subset = nullptr;
+    if (round > 0) {
+      CK(cudaMemcpyAsync(ctx->subset.p, todo.data(), sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, ctx->stream));
+      h2d_bytes += sizeof(int32_t) * (int64_t)m;
+      d_subset = (const int32_t *)ctx->subset.p;
+      /* reset the queue head only */
+      CK(cudaMemsetAsync(&O.cursors[4], 0, sizeof(unsigned long long), ctx->stream));
+    }
+    CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    order_kernel<<<(m + 255) / 256, 256, 0, ctx->stream>>>(d_offs, d_subset, m, (int32_t *)ctx->order.p);
+    fold_kernel<<<(unsigned)grid, T, 0, ctx->stream>>>(ctx->d_energy, F, caps, (char *)ctx->arenas.p, d_seqs,
+                                                      d_offs, (const int32_t *)ctx->order.p, m, O);
+    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    launches += 2;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(h_status.data(), O.status, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->h_small, O.cursors, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    d2h += sizeof(int32_t) * (int64_t)n + 64;
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+    kernel_ms += ms;
+    for (int k = 0; k < 4; k++) used[k] = ctx->h_small[k];
+    todo.clear();
+    for (int i = 0; i < n; i++)
+      if (h_status[i] == ST_ERR_CAPACITY) todo.push_back(i);
+    if (todo.empty() || round >= 5) break;
+    scale *= 4;
+  }
+
+  /* ordered layout on the device, then one copy per array into pinned host memory */
+  int64_t *d_scan = nullptr;
+  size_t scan_bytes = sizeof(int64_t) * (4 * (size_t)(n + 1) + 8);
+  if (int rc = dev_reserve(ctx, ctx->scan, scan_bytes)) return fail(rc);
+  d_scan = (int64_t *)ctx->scan.p;
+  int64_t *d_struct_off = d_scan, *d_db_off = d_scan + (n + 1), *d_step_off = d_scan + 2 * (size_t)(n + 1),
+          *d_ent_base = d_scan + 3 * (size_t)(n + 1), *d_totals = d_scan + 4 * (size_t)(n + 1);
+  CK(cudaEventRecord(ctx->ev0, ctx->stream));
+  scan_kernel<<<1, 1024, 0, ctx->stream>>>(d_offs, n, O, d_struct_off, d_db_off, d_step_off, d_ent_base, d_totals);
+  launches++;
+  CK(cudaMemcpyAsync(ctx->h_small, d_totals, 4 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  d2h += 32;
+  const int64_t nS = ctx->h_small[0], nD = ctx->h_small[1], nT = ctx->h_small[2], nE = ctx->h_small[3];
+  /* device ordered buffer: energy | entry_struct | entry_off | db */
+  size_t o_energy = 0, o_entry = align_up(o_energy + sizeof(int32_t) * (size_t)nS, 256),
+         o_entoff = align_up(o_entry + sizeof(int32_t) * (size_t)nE, 256),
+         o_db = align_up(o_entoff + sizeof(int64_t) * (size_t)(nT + 1), 256),
+         o_end = align_up(o_db + (size_t)nD, 256);
+  if (int rc = dev_reserve(ctx, ctx->ordered, o_end)) return fail(rc);
+  char *dord = (char *)ctx->ordered.p;
+  if (n > 0) {
+    pack_kernel<<<n, 256, 0, ctx->stream>>>(d_offs, n, O, d_struct_off, d_db_off, d_step_off, d_ent_base,
+                                           (int32_t *)(dord + o_energy), dord + o_db,
+                                           (int64_t *)(dord + o_entoff), (int32_t *)(dord + o_entry));
+    launches++;
+  } else {
+    CK(cudaMemsetAsync(dord + o_entoff, 0, sizeof(int64_t), ctx->stream));
+  }
+  CK(cudaEventRecord(ctx->ev1, ctx->stream));
+  CK(cudaGetLastError());
+  /* host block: [ordered part as on the device] status | struct_off | db_off | step_off | counters */
+  size_t h_status_o = o_end, h_soff = align_up(h_status_o + sizeof(int32_t) * (size_t)n, 16),
+         h_doff = h_soff + sizeof(int64_t) * (size_t)(n + 1), h_toff = h_doff + sizeof(int64_t) * (size_t)(n + 1),
+         h_cnt = h_toff + sizeof(int64_t) * (size_t)(n + 1), h_end = h_cnt + sizeof(int64_t) * (size_t)n * CNT_N;
+  if (int rc = host_block_get(ctx, h_end + 64, &R->block)) return fail(rc);
+  char *hb = (char *)R->block.p;
+  CK(cudaMemcpyAsync(hb, dord, o_end, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(hb + h_soff, d_scan, sizeof(int64_t) * 3 * (size_t)(n + 1), cudaMemcpyDeviceToHost, ctx->stream));
+  if (n > 0) CK(cudaMemcpyAsync(hb + h_cnt, O.counters, sizeof(int64_t) * (size_t)n * CNT_N, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  d2h += (int64_t)o_end + (int64_t)sizeof(int64_t) * (3 * (n + 1) + (int64_t)n * CNT_N);
+  float ms2 = 0.f;
+  CK(cudaEventElapsedTime(&ms2, ctx->ev0, ctx->ev1));
+  kernel_ms += ms2;
+  memcpy(hb + h_status_o, h_status.data(), sizeof(int32_t) * (size_t)n);
+  rafft_result &P = R->pub;
+  P.n_seq = n;
+  P.status = (const int32_t *)(hb + h_status_o);
+  P.struct_off = (const int64_t *)(hb + h_soff);
+  P.db_off = (const int64_t *)(hb + h_doff);
+  P.step_off = (const int64_t *)(hb + h_toff);
+  P.energy_dcal = (const int32_t *)(hb + o_energy);
+  P.db = hb + o_db;
+  P.entry_off = (const int64_t *)(hb + o_entoff);
+  P.entry_struct = (const int32_t *)(hb + o_entry);
+  P.counters = (const int64_t *)(hb + h_cnt);
+  P.kernel_ms = kernel_ms;
+  P.kernel_launches = launches;
+  P.h2d_bytes = h2d_bytes;
+  P.d2h_bytes = d2h;
+  *out_res = &R->pub;
+  return RAFFT_OK;
+}
+
+extern "C" {
+
+int rafft_fold_batch(rafft_ctx *ctx, const char *seqs, const int64_t *offs, int32_t n,
+                     const rafft_params *params, rafft_result **out) {
+  if (!ctx) return RAFFT_ERR_ARG;
+  if (!out || !params || n < 0 || (n > 0 && (!seqs || !offs))) { ctx->err = "rafft_fold_batch: bad argument"; return RAFFT_ERR_ARG; }
+  *out = nullptr;
+  CK(cudaSetDevice(ctx->device));
+  static const int64_t zero_offs[1] = {0};
+  if (n == 0) offs = zero_offs;
+  for (int i = 0; i < n; i++)
+    if (offs[i + 1] < offs[i]) { ctx->err = "rafft_fold_batch: offsets must be non-decreasing"; return RAFFT_ERR_ARG; }
+  const int64_t base = offs[0], total = offs[n] - base;
+  if (int rc = dev_reserve(ctx, ctx->seqs, (size_t)total + 16)) return rc;
+  if (int rc = dev_reserve(ctx, ctx->offs, sizeof(int64_t) * (size_t)(n + 1))) return rc;
+  std::vector<int64_t> rel(n + 1);
+  for (int i = 0; i <= n; i++) rel[i] = offs[i] - base;
+  if (total > 0) CK(cudaMemcpyAsync(ctx->seqs.p, seqs + base, (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(ctx->offs.p, rel.data(), sizeof(int64_t) * (size_t)(n + 1), cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return fold_device(ctx, (const char *)ctx->seqs.p, (const int64_t *)ctx->offs.p, rel.data(), n, params, out,
+                     total + (int64_t)sizeof(int64_t) * (n + 1));
+}
+
+int rafft_fold_batch_device(rafft_ctx *ctx, const void *d_seqs, const void *d_offs, int32_t n,
+                            int64_t total_len, int32_t max_len, const rafft_params *params,
+                            rafft_result **out) {
+  if (!ctx) return RAFFT_ERR_ARG;
+  if (!out || !params || n < 0 || (n > 0 && (!d_seqs || !d_offs))) { ctx->err = "rafft_fold_batch_device: bad argument"; return RAFFT_ERR_ARG; }
+  (void)total_len; (void)max_len;
+  *out = nullptr;
+  CK(cudaSetDevice(ctx->device));
+  /* the offsets (8(n+1) bytes) are needed on the host to size the arenas and the result */
+  std::vector<int64_t> h_offs(n + 1, 0);
+  if (n > 0) CK(cudaMemcpy(h_offs.data(), d_offs, sizeof(int64_t) * (size_t)(n + 1), cudaMemcpyDeviceToHost));
+  if (n > 0 && h_offs[0] != 0) { ctx->err = "rafft_fold_batch_device: offs[0] must be 0"; return RAFFT_ERR_ARG; }
+  for (int i = 0; i < n; i++)
+    if (h_offs[i + 1] < h_offs[i]) { ctx->err = "rafft_fold_batch_device: offsets must be non-decreasing"; return RAFFT_ERR_ARG; }
+  return fold_device(ctx, (const char *)d_seqs, (const int64_t *)d_offs, h_offs.data(), n, params, out, 0);
+}
+
+int rafft_eval_structures(rafft_ctx *ctx, const char *seqs, const char *structs, const int64_t *offs,
+                          int32_t n, int32_t *energy_dcal) {
+  if (!ctx) return RAFFT_ERR_ARG;
+  if (n < 0 || (n > 0 && (!seqs || !structs || !offs || !energy_dcal))) { ctx->err = "rafft_eval_structures: bad argument"; return RAFFT_ERR_ARG; }
+  if (n == 0) return RAFFT_OK;
+  CK(cudaSetDevice(ctx->device));
+  const int64_t base = offs[0], total = offs[n] - base;
+  std::vector<int64_t> rel(n + 1);
+  for (int i = 0; i <= n; i++) {
+    rel[i] = offs[i] - base;
+    if (i && rel[i] < rel[i - 1]) { ctx->err = "rafft_eval_structures: offsets must be non-decreasing"; return RAFFT_ERR_ARG; }
+    if (i && rel[i] - rel[i - 1] > 4096) { ctx->err = "rafft_eval_structures: sequence length must be <= 4096"; return RAFFT_ERR_ARG; }
+  }
+  /* seqs | dbs | codes | offs | scratch(2 ints per letter) | energies */
+  size_t o_seq = 0, o_db = align_up((size_t)total, 256), o_code = o_db + align_up((size_t)total, 256),
+         o_offs = o_code + align_up((size_t)total, 256), o_scr = align_up(o_offs + sizeof(int64_t) * (size_t)(n + 1), 256),
+         o_e = align_up(o_scr + sizeof(int32_t) * 2 * (size_t)total, 256), o_end = o_e + sizeof(int32_t) * (size_t)n;
+  if (int rc = dev_reserve(ctx, ctx->evalbuf, o_end)) return rc;
+  char *d = (char *)ctx->evalbuf.p;
+  if (total > 0) {
+    CK(cudaMemcpyAsync(d + o_seq, seqs + base, (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d + o_db, structs + base, (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
+  }
+  CK(cudaMemcpyAsync(d + o_offs, rel.data(), sizeof(int64_t) * (size_t)(n + 1), cudaMemcpyHostToDevice, ctx->stream));
+  const int wpb = 4;
+  eval_kernel<<<(n + wpb - 1) / wpb, wpb * 32, 0, ctx->stream>>>(ctx->d_energy, d + o_seq, d + o_db,
+                                                               (const int64_t *)(d + o_offs), n, (int32_t *)(d + o_scr),
+                                                               (uint8_t *)(d + o_code), (int32_t *)(d + o_e));
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(energy_dcal, d + o_e, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return RAFFT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,202 @@
+"""Python entry points of the folding path, drop-in for the reference's rafft/rafft.py:
+`fold` keeps the signature, defaults and return types of rafft.rafft.fold (:219-239);
+`fold_batch` folds many sequences in one call of the CUDA library.  All of the work
+(correlation, lag ranking, stem scan, energy evaluation, beam search) runs on the GPU
+through the C-ABI in include/rafft_b200.h; this module only marshals arguments/results."""
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+from .utils import Structure, energy_from_dcal
+
+_VALID = frozenset("ACGU")
+
+
+class FoldContext:
+    """One `rafft_ctx` (one CUDA device).  Not thread-safe, like the reference's
+    `unsendable` handle (rafft-rs/src/bindings.rs:10-11)."""
+
+    def __init__(self, device=0, energy_params=None):
+        self._lib = N.lib()
+        self._h = C.c_void_p()
+        ep = C.byref(energy_params) if energy_params is not None else None
+        rc = self._lib.rafft_create(C.byref(self._h), int(device), ep)
+        if rc != N.RAFFT_OK:
+            raise N.NativeError(rc, (self._lib.rafft_last_error(None) or b"").decode())
+        self.device = int(device)
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.rafft_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _err(self, rc):
+        return N.NativeError(rc, (self._lib.rafft_last_error(self._h) or b"").decode())
+
+    # -- raw calls ---------------------------------------------------------------------
+    def fold_raw(self, seq_bytes, offs, params):
+        """seq_bytes: concatenated ASCII letters; offs: int64 numpy array (n+1).
+        Returns a RawResult (numpy copies of the library-owned arrays)."""
+        offs = np.ascontiguousarray(offs, dtype=np.int64)
+        n = len(offs) - 1
+        res = C.POINTER(N.Result)()
+        rc = self._lib.rafft_fold_batch(self._h, seq_bytes, offs.ctypes.data_as(C.POINTER(C.c_int64)),
+                                        n, C.byref(params), C.byref(res))
+        if rc != N.RAFFT_OK:
+            raise self._err(rc)
+        try:
+            return RawResult(res.contents, offs)
+        finally:
+            self._lib.rafft_result_free(res)
+
+    def fold_raw_device(self, d_seqs_ptr, d_offs_ptr, n, total_len, max_len, params, keep=True):
+        """Inputs already on this context's device (raw device pointers)."""
+        res = C.POINTER(N.Result)()
+        rc = self._lib.rafft_fold_batch_device(self._h, C.c_void_p(d_seqs_ptr), C.c_void_p(d_offs_ptr),
+                                               n, total_len, max_len, C.byref(params), C.byref(res))
+        if rc != N.RAFFT_OK:
+            raise self._err(rc)
+        try:
+            return RawResult(res.contents, None, copy=keep)
+        finally:
+            self._lib.rafft_result_free(res)
+
+    def eval_structures(self, seqs, structs):
+        "integer energies (dcal/mol) of whole structures; replaces fold_compound.eval_structure"
+        assert len(seqs) == len(structs)
+        n = len(seqs)
+        offs = np.zeros(n + 1, dtype=np.int64)
+        for i, (s, d) in enumerate(zip(seqs, structs)):
+            if len(s) != len(d):
+                raise ValueError("sequence and structure %d differ in length" % i)
+            offs[i + 1] = offs[i] + len(s)
+        out = np.zeros(max(n, 1), dtype=np.int32)
+        rc = self._lib.rafft_eval_structures(self._h, "".join(seqs).encode(), "".join(structs).encode(),
+                                             offs.ctypes.data_as(C.POINTER(C.c_int64)), n,
+                                             out.ctypes.data_as(C.POINTER(C.c_int32)))
+        if rc != N.RAFFT_OK:
+            raise self._err(rc)
+        return out[:n]
+
+
+def _np(ptr, count, dtype):
+    if count == 0:
+        return np.zeros(0, dtype=dtype)
+    return np.ctypeslib.as_array(ptr, shape=(count,)).view(dtype)
+
+
+class RawResult:
+    """Arrays of one rafft_result (see include/rafft_b200.h)."""
+
+    def __init__(self, r, offs, copy=True):
+        n = r.n_seq
+        self.n_seq = n
+        self.kernel_ms = r.kernel_ms
+        self.kernel_launches = r.kernel_launches
+        self.h2d_bytes, self.d2h_bytes = r.h2d_bytes, r.d2h_bytes
+        self.status = _np(r.status, n, np.int32).copy()
+        self.struct_off = _np(r.struct_off, n + 1, np.int64).copy()
+        self.db_off = _np(r.db_off, n + 1, np.int64).copy()
+        self.step_off = _np(r.step_off, n + 1, np.int64).copy()
+        self.counters = _np(r.counters, n * N.CNT_N, np.int64).reshape(n, N.CNT_N).copy()
+        self.n_struct = int(self.struct_off[n])
+        if not copy:
+            return
+        nS, nD, nT = int(self.struct_off[n]), int(self.db_off[n]), int(self.step_off[n])
+        self.energy = _np(r.energy_dcal, nS, np.int32).copy()
+        self.db = C.string_at(r.db, nD) if nD else b""
+        self.entry_off = _np(r.entry_off, nT + 1, np.int64).copy()
+        self.entry_struct = _np(r.entry_struct, int(self.entry_off[nT]) if nT else 0, np.int32).copy()
+        if offs is not None:
+            self.lengths = np.diff(offs)
+        else:
+            ns = np.diff(self.struct_off)
+            self.lengths = np.where(ns > 0, np.diff(self.db_off) // np.maximum(ns, 1), 0)
+
+    def steps(self, i):
+        """sequence i -> list of steps, each a list of (dot-bracket, E_dcal)."""
+        L = int(self.lengths[i])
+        s0, d0 = int(self.struct_off[i]), int(self.db_off[i])
+        out = []
+        for t in range(int(self.step_off[i]), int(self.step_off[i + 1])):
+            step = []
+            for e in range(int(self.entry_off[t]), int(self.entry_off[t + 1])):
+                k = int(self.entry_struct[e])
+                step.append((self.db[d0 + k * L:d0 + (k + 1) * L].decode(), int(self.energy[s0 + k])))
+            out.append(step)
+        return out
+
+
+def make_params(nb_mode=100, max_stack=1, max_branch=100, min_hp=3, min_nrj=0.0, traj=False,
+                temp=37.0, gc_wei=3.0, au_wei=2.0, gu_wei=1.0):
+    return N.Params(int(nb_mode), int(max_stack), int(max_branch), int(min_hp), 1 if traj else 0,
+                    float(min_nrj), float(temp), float(gc_wei), float(au_wei), float(gu_wei))
+
+
+_contexts = {}
+
+
+def get_context(device=0):
+    "process-wide context of a device, created on first use"
+    ctx = _contexts.get(device)
+    if ctx is None:
+        ctx = _contexts[device] = FoldContext(device)
+    return ctx
+
+
+def _structures(step):
+    out = []
+    for db, e in step:
+        st = Structure()
+        st.str_struct = db
+        st.energy_dcal = e
+        st.energy = energy_from_dcal(e)
+        out.append(st)
+    return out
+
+
+def _check_letters(sequence):
+    for ch in sequence:
+        if ch not in _VALID:
+            # the reference fails with KeyError in prep_sequence (rafft/utils.py:73-80); its
+            # `N` rows are all-zero and ViennaRNA treats N specially: not supported here
+            raise KeyError(ch)
+
+
+def fold_batch(sequences, nb_mode=100, max_stack=1, max_branch=100, min_hp=3, min_nrj=0.0,
+               traj=False, temp=37.0, gc_wei=3.0, au_wei=2.0, gu_wei=1.0, device=0, context=None):
+    """Fold many sequences in one library call.  Returns one `fold`-style result per
+    sequence (list of Structure, or (list, trajectory) with traj=True)."""
+    sequences = list(sequences)
+    for s in sequences:
+        _check_letters(s)
+        if len(s) == 0:
+            raise ValueError("empty sequence")
+    ctx = context if context is not None else get_context(device)
+    offs = np.zeros(len(sequences) + 1, dtype=np.int64)
+    np.cumsum([len(s) for s in sequences], out=offs[1:])
+    params = make_params(nb_mode, max_stack, max_branch, min_hp, min_nrj, traj, temp, gc_wei,
+                         au_wei, gu_wei)
+    raw = ctx.fold_raw("".join(sequences).encode(), offs, params)
+    out = []
+    for i in range(len(sequences)):
+        if raw.status[i] != N.RAFFT_OK:
+            raise N.NativeError(int(raw.status[i]), "sequence %d could not be folded" % i)
+        steps = raw.steps(i)
+        final = _structures(steps[-1])
+        out.append((final, [_structures(s) for s in steps]) if traj else final)
+    return out
+
+
+def fold(sequence, nb_mode=100, max_stack=1, max_branch=100, min_hp=3, min_nrj=0.0, traj=False,
+         temp=37.0, gc_wei=3.0, au_wei=2.0, gu_wei=1.0):
+    "fold a given sequence (same arguments, defaults and return value as the reference)"
+    return fold_batch([sequence], nb_mode, max_stack, max_branch, min_hp, min_nrj, traj, temp,
+                      gc_wei, au_wei, gu_wei)[0]
