@@ -73,6 +73,7 @@ enum {
   RAFFT_CNT_UNIQ_W_CORR,  /* pair-weight accumulations actually performed */
   RAFFT_CNT_UNIQ_W_SCAN,  /* scan positions actually visited */
   RAFFT_CNT_COMBOS,       /* stem combinations enumerated (itertools.product items) */
+  RAFFT_CNT_NODE_POS,     /* sum over the reference's create_childs calls of the region length Lv */
   RAFFT_CNT_N
 };
 

@@ -120,7 +120,7 @@ struct OutBuf {
 };
 
 enum { CNT_STEPS = 0, CNT_NODE_EXP, CNT_W_CORR, CNT_W_SCAN, CNT_N_EVAL, CNT_UNIQ_NODES,
-       CNT_UNIQ_W_CORR, CNT_UNIQ_W_SCAN, CNT_COMBOS, CNT_N };
+       CNT_UNIQ_W_CORR, CNT_UNIQ_W_SCAN, CNT_COMBOS, CNT_NODE_POS, CNT_N };
 
 enum { ST_OK = 0, ST_ERR_SEQ = 2, ST_ERR_CAPACITY = 4 };
 
@@ -823,6 +823,7 @@ struct Fold {
         for (int k = 0; k < S.nl_n; k++) {
           const NodeRec &nd = A.node[A.nlist[S.nl_off + k]];
           sh->cnt[CNT_NODE_EXP] += 1;
+          sh->cnt[CNT_NODE_POS] += nd.lv;
           sh->cnt[CNT_W_CORR] += (int64_t)nd.lv * (nd.lv + 1) / 2;
           sh->cnt[CNT_W_SCAN] += nd.w_scan;
           sh->cnt[CNT_N_EVAL] += nd.n_pos;

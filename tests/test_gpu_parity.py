@@ -1,0 +1,208 @@
+"""Parity of the CUDA path (through the C-ABI, rafft_b200/librafft_b200.so) with the oracle
+and with the reference's golden vectors.  Bar: bit-exact -- same dot-brackets, same integer
+energies (dcal/mol), same trajectory order."""
+import os
+import random
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT, parse_rafft_text
+from rafft_b200.synth import config_batch, splitmix_seq
+
+pytestmark = pytest.mark.gpu
+
+
+def gpu_steps(ctx, seqs, **kw):
+    from rafft_b200 import rafft as R
+    p = dict(nb_mode=100, max_stack=1, max_branch=1000, min_hp=3, min_nrj=0.0, gc=3.0, au=2.0, gu=1.0)
+    p.update(kw)
+    offs = np.zeros(len(seqs) + 1, dtype=np.int64)
+    np.cumsum([len(s) for s in seqs], out=offs[1:])
+    prm = R.make_params(p["nb_mode"], p["max_stack"], p["max_branch"], p["min_hp"], p["min_nrj"], True, 37.0,
+                        p["gc"], p["au"], p["gu"])
+    raw = ctx.fold_raw("".join(seqs).encode(), offs, prm)
+    assert (raw.status == 0).all(), raw.status
+    return [raw.steps(i) for i in range(len(seqs))], raw
+
+
+def test_native_library_is_loaded(ctx):
+    "the GPU tier runs the in-tree CUDA library, not a fallback"
+    maps = open("/proc/self/maps").read()
+    assert "librafft_b200.so" in maps
+
+
+# ---- (d) energy evaluator --------------------------------------------------------------
+def test_eval_structures_energy_kat(ctx, energy_kat, kernel_kat):
+    seqs = [s for s, _, _ in energy_kat]
+    dbs = [d for _, d, _ in energy_kat]
+    got = ctx.eval_structures(seqs, dbs)
+    want = np.array([e for _, _, e in energy_kat], dtype=np.int32)
+    assert (got == want).all(), np.nonzero(got != want)[0][:5]
+    k = kernel_kat["vrna_eval"]
+    pt = k["pt_1based"]
+    db = "".join("." if pt[i] == 0 else "(" if pt[i] > i else ")" for i in range(1, pt[0] + 1))
+    assert ctx.eval_structures([k["seq"]], [db])[0] == -2580
+
+
+def test_eval_structures_vs_oracle_random(ctx, oracle):
+    "random structures taken from oracle trajectories + malformed input"
+    seqs, dbs = [], []
+    for k in range(40):
+        s = splitmix_seq(400 + k, 40 + 5 * k)
+        for st in oracle.fold(s, 50, 5, 100)[-1]:
+            seqs.append(s)
+            dbs.append(st[0])
+    got = ctx.eval_structures(seqs, dbs)
+    assert [int(g) for g in got] == [oracle.eval_db(s, d) for s, d in zip(seqs, dbs)]
+    bad = ctx.eval_structures(["GGGAAACCC", "GGGAAACCC", "GGGAAACCC"], ["(((...)).", "((.....))", "(((...)))"])
+    assert bad[0] == -(2 ** 31) and bad[1] == oracle.eval_db("GGGAAACCC", "((.....))")
+
+
+# ---- (a)-(c),(e) whole path against golden files ------------------------------------------
+@pytest.mark.parametrize("name,kw", [("rafft.out", dict(nb_mode=100, max_stack=5)),
+                                     ("rafft_20.out", dict(nb_mode=100, max_stack=20)),
+                                     ("analysis_n50_ms5.txt", dict(nb_mode=50, max_stack=5))])
+def test_example_files(ctx, name, kw):
+    from rafft_b200.utils import energy_from_dcal
+    seq, gold = parse_rafft_text(os.path.join(GOLDEN, name))
+    steps = gpu_steps(ctx, [seq], **kw)[0][0]
+    got = [[(db, ("%6.1f" % energy_from_dcal(e)).strip()) for db, e in st] for st in steps]
+    assert got == [[(db, e.strip()) for db, e in st] for st in gold]
+
+
+def test_reference_python_trajectories(ctx, ref_folds):
+    "62 trajectories of the unmodified reference Python, incl. edge cases (L=1, polyA, mb=1, ...)"
+    by_params = {}
+    for c in ref_folds:
+        by_params.setdefault(tuple(sorted(c["params"].items())), []).append(c)
+    for key, cases in by_params.items():
+        got, _ = gpu_steps(ctx, [c["seq"] for c in cases], **dict(key))
+        for c, g in zip(cases, got):
+            assert g == c["steps"], c["name"]
+
+
+def test_kernel_kats_through_the_path(ctx, kernel_kat, oracle):
+    """The Rust stem-scan/correlation KAT sequences: the first folding step of the CUDA path
+    must pick exactly the stems the oracle's auto_cor + window_slide produce."""
+    for seq in (kernel_kat["consecutive_pairs"]["seq"], kernel_kat["autocorrelation"]["seq"],
+                kernel_kat["consecutive_pairs_split"]["seq"]):
+        for n in (1, 3, 10, 100):
+            assert gpu_steps(ctx, [seq], nb_mode=n, max_stack=30)[0][0] == oracle.fold(seq, n, 30, 1000)
+
+
+# ---- batches vs oracle -----------------------------------------------------------------
+def test_batch_cfg2_sample_vs_oracle(ctx, oracle):
+    "every 20th sequence of the 10k benchmark batch at -n 100 -ms 50 (BASELINE config 2)"
+    seqs = config_batch("cfg2")[::20]
+    got, raw = gpu_steps(ctx, seqs, nb_mode=100, max_stack=50)
+    want, cnt = oracle.fold_batch(seqs, 100, 50, 1000)
+    bad = [i for i in range(len(seqs)) if got[i] != want[i]]
+    assert not bad, bad[:5]
+    # reference-formulation work counters agree too
+    assert (raw.counters[:, :5] == cnt[:, :5]).all() and (raw.counters[:, 8:10] == cnt[:, 8:10]).all()
+
+
+def test_batch_cfg3_sample_vs_oracle(ctx, oracle):
+    "-n 200 -ms 200 (BASELINE config 3) on a sample"
+    seqs = config_batch("cfg2")[7::250]
+    got, _ = gpu_steps(ctx, seqs, nb_mode=200, max_stack=200)
+    want, _ = oracle.fold_batch(seqs, 200, 200, 1000)
+    assert got == want
+
+
+def test_random_parameters_vs_oracle(ctx, oracle):
+    rnd = random.Random(4242)
+    for k in range(25):
+        kw = dict(nb_mode=rnd.choice([1, 5, 50, 100, 200]), max_stack=rnd.choice([1, 2, 10, 50]),
+                  max_branch=rnd.choice([1, 7, 100, 1000]), min_hp=rnd.choice([0, 3, 3, 5]),
+                  min_nrj=rnd.choice([0.0, 0.0, -0.6, 0.35]),
+                  **rnd.choice([dict(), dict(gc=1.0, au=1.0, gu=1.0), dict(gc=2.5, au=1.5, gu=0.5)]))
+        seqs = [splitmix_seq(7000 + 31 * k + j, rnd.choice([1, 2, 9, 33, 70, 121, 200])) for j in range(12)]
+        got, _ = gpu_steps(ctx, seqs, **kw)
+        want, _ = oracle.fold_batch(seqs, **kw)
+        assert got == want, kw
+
+
+def test_edge_cases(ctx, oracle):
+    from rafft_b200 import _native as N
+    from rafft_b200 import rafft as R
+    seqs = ["G", "GC", "A" * 50, "GC" * 40, "G" * 45 + "AAAA" + "C" * 45, "GGGAAACCC"]
+    got, _ = gpu_steps(ctx, seqs, nb_mode=100, max_stack=10)
+    assert got == oracle.fold_batch(seqs, 100, 10, 1000)[0]
+    # empty batch
+    raw = ctx.fold_raw(b"", np.zeros(1, dtype=np.int64), R.make_params(traj=True))
+    assert raw.n_seq == 0 and raw.n_struct == 0
+    # a bad letter fails that sequence only (reference: KeyError), neighbours are unaffected
+    offs = np.array([0, 9, 18, 27], dtype=np.int64)
+    raw = ctx.fold_raw(b"GGGAAACCCGGGANACCCGGGAAACCC", offs, R.make_params(max_stack=3, traj=True))
+    assert list(raw.status) == [0, N.RAFFT_ERR_SEQ, 0] and raw.steps(0) == raw.steps(2) != []
+    # unsupported arguments are refused, not approximated
+    for bad in (dict(temp=25.0), dict(gc_wei=0.3), dict(max_stack=0)):
+        with pytest.raises(N.NativeError):
+            ctx.fold_raw(b"GGGAAACCC", np.array([0, 9], dtype=np.int64), R.make_params(**bad))
+
+
+def test_traj_off_returns_final_beam(ctx):
+    from rafft_b200 import fold_batch
+    seqs = config_batch("cfg2", 40)
+    a = fold_batch(seqs, 100, 20, 1000, traj=False, context=ctx)
+    b = fold_batch(seqs, 100, 20, 1000, traj=True, context=ctx)
+    for x, (fin, tr) in zip(a, b):
+        assert [(s.str_struct, s.energy_dcal) for s in x] == [(s.str_struct, s.energy_dcal) for s in fin]
+        assert [(s.str_struct, s.energy_dcal) for s in tr[-1]] == [(s.str_struct, s.energy_dcal) for s in fin]
+
+
+def test_long_sequences_vs_oracle(ctx, oracle):
+    "1000-nt and a 3000-nt (config 4 scale) sequence at reduced -ms so the oracle ends in seconds"
+    seqs = [splitmix_seq(3000, 3000), splitmix_seq(1000, 1000)]
+    got, _ = gpu_steps(ctx, seqs, nb_mode=200, max_stack=10)
+    assert got == oracle.fold_batch(seqs, 200, 10, 1000)[0]
+
+
+# ---- size-independent properties at full size ------------------------------------------------
+def test_full_batch_properties(ctx):
+    "all 10k sequences of config 2: structural invariants + energies re-derived by the evaluator kernel"
+    seqs = config_batch("cfg2")
+    from rafft_b200 import rafft as R
+    offs = np.zeros(len(seqs) + 1, dtype=np.int64)
+    np.cumsum([len(s) for s in seqs], out=offs[1:])
+    raw = ctx.fold_raw("".join(seqs).encode(), offs, R.make_params(100, 50, 1000, traj=False))
+    assert (raw.status == 0).all()
+    ns = np.diff(raw.struct_off)
+    assert (ns >= 1).all() and (ns <= 50).all()
+    ev_s, ev_d, ev_e = [], [], []
+    for i in range(0, len(seqs), 7):
+        final = raw.steps(i)[-1]
+        es = [e for _, e in final]
+        assert es == sorted(es)                       # beam sorted by energy
+        assert len(set(db for db, _ in final)) == len(final)  # no duplicates (global seen set)
+        for db, e in final:
+            assert len(db) == len(seqs[i]) and db.count("(") == db.count(")")
+            ev_s.append(seqs[i]); ev_d.append(db); ev_e.append(e)
+    got = ctx.eval_structures(ev_s, ev_d)               # incremental dE sums == full evaluation
+    assert (got == np.array(ev_e, dtype=np.int32)).all()
+    # determinism / idempotence
+    raw2 = ctx.fold_raw("".join(seqs).encode(), offs, R.make_params(100, 50, 1000, traj=False))
+    assert raw2.db == raw.db and (raw2.energy == raw.energy).all()
+
+
+# ---- the drop-in surface ---------------------------------------------------------------
+def test_cli_reproduces_example_file():
+    seq = open(os.path.join(GOLDEN, "rafft.out")).readline().strip()
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bin", "rafft"), "-s", seq, "-ms", "5", "--traj"],
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    assert out.stdout == open(os.path.join(GOLDEN, "rafft.out")).read()
+
+
+def test_fold_api_like_reference(ctx):
+    from rafft_b200 import fold
+    seq = open(os.path.join(GOLDEN, "rafft_20.out")).readline().strip()
+    final, traj = fold(seq, max_stack=20, traj=True, max_branch=1000)
+    _, gold = parse_rafft_text(os.path.join(GOLDEN, "rafft_20.out"))
+    assert [s.str_struct for s in final] == [db for db, _ in gold[-1]]
+    assert ["%6.1f" % s.energy for s in traj[1]] == ["%6.1f" % float(e) for _, e in gold[1]]
+    assert isinstance(fold(seq), list) and len(fold(seq)) == 1

@@ -38,7 +38,7 @@ def kernel_kat():
     enc = open(REF + "/rafft-rs/src/encoding.rs").read()
     t = enc[enc.index("fn test_consecutivepairs"):]
     seq14 = re.search(r'let sequence = "([ACGU]+)"', t).group(1)
-    split16 = re.search(r'let tobesplit = "([ACGU]+)"', t).group(1)
+    split16 = re.search(r'^\s*let tobesplit = "([ACGU]+)"', t, re.M).group(1)  # not the commented-out one
     cp = re.findall(r"(encoded|splitenc)\.consecutive_pairs_at_lag\((\d+), (\d+)\), "
                     r"\((\d+), (\d+), (\d+), ([\d.]+)\)", t)
     whole = [[int(l), int(mh), int(a1), int(b1), int(c1), float(s)]
