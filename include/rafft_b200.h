@@ -74,6 +74,8 @@ enum {
   RAFFT_CNT_UNIQ_W_SCAN,  /* scan positions actually visited */
   RAFFT_CNT_COMBOS,       /* stem combinations enumerated (itertools.product items) */
   RAFFT_CNT_NODE_POS,     /* sum over the reference's create_childs calls of the region length Lv */
+  RAFFT_CNT_T0_NS,        /* device globaltimer when the fold of this sequence started ... */
+  RAFFT_CNT_T1_NS,        /* ... and ended (diagnostics: schedule / tail analysis) */
   RAFFT_CNT_N
 };
 

@@ -120,7 +120,7 @@ struct OutBuf {
 };
 
 enum { CNT_STEPS = 0, CNT_NODE_EXP, CNT_W_CORR, CNT_W_SCAN, CNT_N_EVAL, CNT_UNIQ_NODES,
-       CNT_UNIQ_W_CORR, CNT_UNIQ_W_SCAN, CNT_COMBOS, CNT_NODE_POS, CNT_N };
+       CNT_UNIQ_W_CORR, CNT_UNIQ_W_SCAN, CNT_COMBOS, CNT_NODE_POS, CNT_T0_NS, CNT_T1_NS, CNT_N };
 
 enum { ST_OK = 0, ST_ERR_SEQ = 2, ST_ERR_CAPACITY = 4 };
 
@@ -144,6 +144,7 @@ struct Exec {
   RF_FN static double dmul(double a, double b) { return __dmul_rn(a, b); }
   RF_FN static double ddiv(double a, double b) { return __ddiv_rn(a, b); }
   RF_FN static unsigned long long dbits(double a) { return (unsigned long long)__double_as_longlong(a); }
+  RF_FN static long long now_ns() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return (long long)t; }
 };
 #define RF_PAR_BEGIN(i, n) \
   Exec::sync();            \
@@ -177,6 +178,7 @@ struct Exec {
   static double dmul(double a, double b) { volatile double r = a * b; return r; }
   static double ddiv(double a, double b) { volatile double r = a / b; return r; }
   static unsigned long long dbits(double a) { unsigned long long u; memcpy(&u, &a, 8); return u; }
+  static long long now_ns() { return 0; }
 };
 /* Iterations of a phase must be independent: the emulation runs them forward or reversed. */
 #define RF_PAR_BEGIN(i, n)                                   \
@@ -725,6 +727,7 @@ struct Fold {
       sh->n_seen = 0; sh->n_todo = 0; sh->n_expand = 0; sh->beam_n = 0; sh->n_new = 0;
       sh->nb_branch = 0; sh->n_steps = 0; sh->n_traj = 0;
       for (int k = 0; k < CNT_N; k++) sh->cnt[k] = 0;
+      sh->cnt[CNT_T0_NS] = Exec::now_ns();
       if (L > caps.L_max) sh->status = ST_ERR_CAPACITY;
       else if (L < 1) sh->status = ST_ERR_SEQ; /* the reference cannot fold an empty sequence */
     RF_SINGLE_END
@@ -1101,6 +1104,7 @@ struct Fold {
       out.seq_db[si] = (int64_t)d0;
       out.seq_step[si] = (int64_t)t0; out.seq_nstep[si] = nstep;
       out.seq_entry[si] = (int64_t)e0;
+      sh->cnt[CNT_T1_NS] = Exec::now_ns();
       for (int k = 0; k < CNT_N; k++) out.counters[(size_t)si * CNT_N + k] = sh->cnt[k];
       sh->tmp0 = nstruct;
     RF_SINGLE_END
