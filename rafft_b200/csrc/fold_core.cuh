@@ -1,5 +1,5 @@
 /*
- * fold_core.cuh -- the RAFFT folding hot path as ONE cooperative thread block per sequence.
+ * fold_core.cuh -- the RAFFT folding hot path: one thread block (1..8 warps) per sequence.
  *
  * What the reference does per sequence (rafft/rafft.py:156-216 bfs_pairs, :112-153
  * create_childs, :86-109 find_best_consecutives, :36-83 window_slide; rafft/utils.py:115-132
@@ -13,9 +13,13 @@
  * the max_branch cut and the stable energy sort then run on integers only and reproduce
  * the reference's order exactly.
  *
- * The code is written as uniform control flow + `par_for` / `single` phases (each phase is
- * bracketed by block barriers).  tests/emu compiles this same file for the host with
- * blockDim = 1 to check the logic without a GPU; that build is test-only.
+ * Two scopes of parallelism:
+ *   warp tasks   one node expansion per warp (RF_W* phases, __syncwarp only): bit-parallel
+ *                one-hot correlation, bitonic lag ranking, per-lag stem scan over set bits,
+ *                loop-energy change of every stem, stable candidate sort;
+ *   block phases the beam logic (RF_PAR / RF_SINGLE phases bracketed by block barriers).
+ * tests/emu compiles this same file for the host with one thread per scope to check the
+ * logic without a GPU; that build is test-only.
  */
 #pragma once
 #include <stdint.h>
@@ -27,7 +31,7 @@
 #define RF_HD __host__ __device__ inline
 #else
 #define RF_FN inline
-#define RF_NOINLINE
+#define RF_NOINLINE inline
 #define RF_HD inline
 #include <math.h>
 #endif
@@ -66,6 +70,11 @@ struct Caps {
   int32_t new_cap;           /* >= max_branch + max_stack + 1 */
   int32_t step_cap;          /* folding steps */
   int32_t todo_cap;
+  int32_t chunk_cap;         /* stem combinations examined per block phase */
+  int32_t nwarps;            /* warps per block = concurrent node expansions */
+  int32_t key_cap;           /* per-warp sort keys: pow2 >= max(2*L_max, nb_mode) */
+  int32_t mask_words;        /* 32-bit words per one-hot mask (L_max/32 + 2) */
+  int32_t wscratch_bytes;    /* per-warp expansion scratch */
   int64_t arena_bytes;
 };
 
@@ -78,6 +87,7 @@ struct NodeRec {
   int32_t n_ranked, n_pos;  /* lags scanned / lags with a stem (reference work counters) */
   int64_t w_scan;           /* sum of ceil(d/2) over the ranked lags */
   uint64_t hash;
+  int32_t nht_slot, pad_;   /* slot in the unique-loop table (for the clean-up) */
 };
 
 struct Cand {
@@ -125,13 +135,23 @@ enum { CNT_STEPS = 0, CNT_NODE_EXP, CNT_W_CORR, CNT_W_SCAN, CNT_N_EVAL, CNT_UNIQ
 enum { ST_OK = 0, ST_ERR_SEQ = 2, ST_ERR_CAPACITY = 4 };
 
 /* ------------------------------------------------------------------------------------ */
-/* Execution policy: CUDA thread block, or a single host thread (tests/emu only).        */
+/* Execution policy: CUDA thread block of 1..8 warps, or a single host thread             */
+/* (tests/emu only).  Block scope: tid/nthreads/sync.  Warp scope: lane/warp/wsync.       */
 #ifdef __CUDACC__
 struct Exec {
   RF_FN static int tid() { return threadIdx.x; }
   RF_FN static int nthreads() { return blockDim.x; }
+  RF_FN static int stride() { return blockDim.x; } /* of hand-written block-strided loops */
+  RF_FN static int lane() { return threadIdx.x & 31; }
+  RF_FN static int lanes() { return 32; }
+  RF_FN static int warp() { return threadIdx.x >> 5; }
+  RF_FN static int nwarps() { return blockDim.x >> 5; }
   RF_FN static void sync() { __syncthreads(); }
+  RF_FN static void wsync() { __syncwarp(); }
   RF_FN static int atomic_add(int *p, int v) { return atomicAdd(p, v); }
+  RF_FN static unsigned atomic_or(unsigned *p, unsigned v) { return atomicOr(p, v); }
+  RF_FN static int atomic_min(int *p, int v) { return atomicMin(p, v); }
+  RF_FN static int atomic_max(int *p, int v) { return atomicMax(p, v); }
   RF_FN static unsigned long long atomic_add64(unsigned long long *p, unsigned long long v) {
     return atomicAdd(p, v);
   }
@@ -145,6 +165,38 @@ struct Exec {
   RF_FN static double ddiv(double a, double b) { return __ddiv_rn(a, b); }
   RF_FN static unsigned long long dbits(double a) { return (unsigned long long)__double_as_longlong(a); }
   RF_FN static long long now_ns() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return (long long)t; }
+  RF_FN static int popc(unsigned x) { return __popc(x); }
+  RF_FN static int ffs(unsigned x) { return __ffs((int)x); }
+  /* bits [b, b+32) of the 64-bit value hi:lo, 0 <= b < 32 */
+  RF_FN static unsigned funnel_r(unsigned lo, unsigned hi, int b) { return __funnelshift_r(lo, hi, b); }
+  /* Block-wide exclusive prefix sum of 0/1 flags (n <= capacity of flag/pref); returns the
+   * total.  Must be called by every thread of the block; `wsum` = nwarps+1 ints of shared
+   * memory.  Ends with a barrier, so pref[] and the total are visible to all threads. */
+  __device__ __noinline__ static int scan_flags(const int *flag, int *pref, int n, int *wsum) {
+    const int T = blockDim.x, t = threadIdx.x;
+    const int per = (n + T - 1) / T;
+    const int lo = min(n, t * per), hi = min(n, lo + per);
+    __syncthreads();
+    int c = 0;
+    for (int i = lo; i < hi; i++) c += flag[i];
+    int inc = c;
+    for (int d = 1; d < 32; d <<= 1) {
+      int v = __shfl_up_sync(0xffffffffu, inc, d);
+      if ((t & 31) >= d) inc += v;
+    }
+    if ((t & 31) == 31) wsum[t >> 5] = inc;
+    __syncthreads();
+    int base = 0, total = 0;
+    for (int w = 0; w < (T >> 5); w++) {
+      int v = wsum[w];
+      if (w < (t >> 5)) base += v;
+      total += v;
+    }
+    int run = base + inc - c;
+    for (int i = lo; i < hi; i++) { pref[i] = run; run += flag[i]; }
+    __syncthreads();
+    return total;
+  }
 };
 #define RF_PAR_BEGIN(i, n) \
   Exec::sync();            \
@@ -158,14 +210,35 @@ struct Exec {
 #define RF_SINGLE_END \
   }                   \
   Exec::sync();
+#define RF_WPAR_BEGIN(i, n) \
+  Exec::wsync();            \
+  for (int i = Exec::lane(); i < (n); i += 32) {
+#define RF_WPAR_END \
+  }                 \
+  Exec::wsync();
+#define RF_WSINGLE_BEGIN \
+  Exec::wsync();         \
+  if (Exec::lane() == 0) {
+#define RF_WSINGLE_END \
+  }                    \
+  Exec::wsync();
 #else
 struct Exec {
   static int &order() { static int o = 0; return o; } /* 0 forward, 1 reverse iteration */
   static int tid() { return 0; }
   static int &emu_threads() { static int t = 32; return t; } /* chunk width of the emulation */
   static int nthreads() { return emu_threads(); }
+  static int stride() { return 1; }
+  static int lane() { return 0; }
+  static int lanes() { return 1; }
+  static int warp() { return 0; }
+  static int nwarps() { return 1; }
   static void sync() {}
+  static void wsync() {}
   static int atomic_add(int *p, int v) { int o = *p; *p += v; return o; }
+  static unsigned atomic_or(unsigned *p, unsigned v) { unsigned o = *p; *p |= v; return o; }
+  static int atomic_min(int *p, int v) { int o = *p; if (v < o) *p = v; return o; }
+  static int atomic_max(int *p, int v) { int o = *p; if (v > o) *p = v; return o; }
   static unsigned long long atomic_add64(unsigned long long *p, unsigned long long v) {
     unsigned long long o = *p; *p += v; return o;
   }
@@ -179,6 +252,16 @@ struct Exec {
   static double ddiv(double a, double b) { volatile double r = a / b; return r; }
   static unsigned long long dbits(double a) { unsigned long long u; memcpy(&u, &a, 8); return u; }
   static long long now_ns() { return 0; }
+  static int popc(unsigned x) { return __builtin_popcount(x); }
+  static int ffs(unsigned x) { return __builtin_ffs((int)x); }
+  static unsigned funnel_r(unsigned lo, unsigned hi, int b) {
+    return b ? (lo >> b) | (hi << (32 - b)) : lo;
+  }
+  static int scan_flags(const int *flag, int *pref, int n, int *) {
+    int run = 0;
+    for (int i = 0; i < n; i++) { pref[i] = run; run += flag[i]; }
+    return run;
+  }
 };
 /* Iterations of a phase must be independent: the emulation runs them forward or reversed. */
 #define RF_PAR_BEGIN(i, n)                                   \
@@ -187,6 +270,10 @@ struct Exec {
 #define RF_PAR_END }
 #define RF_SINGLE_BEGIN {
 #define RF_SINGLE_END }
+#define RF_WPAR_BEGIN(i, n) RF_PAR_BEGIN(i, n)
+#define RF_WPAR_END }
+#define RF_WSINGLE_BEGIN {
+#define RF_WSINGLE_END }
 #endif
 
 /* ------------------------------------------------------------------------------------ */
@@ -221,7 +308,7 @@ RF_FN int e_loglen(const EnergyView &ev, const int32_t *arr, int u) {
   return u <= 30 ? arr[u] : arr[30] + ev.P->logterm[u < 4096 ? u : 4095];
 }
 
-RF_FN int e_hairpin(const EnergyView &ev, int i, int j) {
+RF_NOINLINE int e_hairpin(const EnergyView &ev, int i, int j) {
   const DevEnergy *P = ev.P;
   int u = j - i - 1;
   int e = e_loglen(ev, P->hairpin, u);
@@ -245,7 +332,7 @@ RF_FN int e_hairpin(const EnergyView &ev, int i, int j) {
   return e + P->mmH[t * 16 + ev.s[i + 1] * 4 + ev.s[j - 1]];
 }
 
-RF_FN int e_interior(const EnergyView &ev, int i, int j, int p, int q) {
+RF_NOINLINE int e_interior(const EnergyView &ev, int i, int j, int p, int q) {
   const DevEnergy *P = ev.P;
   const uint8_t *s = ev.s;
   int n1 = p - i - 1, n2 = j - q - 1;
@@ -301,7 +388,7 @@ RF_FN int e_extstem(const EnergyView &ev, int p, int q) {
 
 /* Energy of the loop closed by (ci,cj) (ci < 0: exterior) whose branches are, in order,
  * br[lo1..hi1), then the extra pair (xp,xq) if xp >= 0, then br[lo2..hi2); `unp` unpaired. */
-RF_FN int loop_energy(const EnergyView &ev, int ci, int cj, const int16_t *br, int lo1, int hi1,
+RF_NOINLINE int loop_energy(const EnergyView &ev, int ci, int cj, const int16_t *br, int lo1, int hi1,
                       int xp, int xq, int lo2, int hi2, int unp) {
   int nb = (hi1 - lo1) + (xp >= 0 ? 1 : 0) + (hi2 - lo2);
   if (ci < 0) {
@@ -331,9 +418,10 @@ RF_FN int loop_energy(const EnergyView &ev, int ci, int cj, const int16_t *br, i
   for (int k = lo2; k < hi2; k++) e += e_mlstem(ev, br[2 * k], br[2 * k + 1]);
   return e;
 }
-
 /* ------------------------------------------------------------------------------------ */
-/* Per-block working memory, carved from one arena.                                      */
+/* Per-block working memory, carved from one arena (global memory, L1/L2 resident).       */
+struct SeenEnt { uint64_t lo, hi; };
+
 struct Arena {
   uint8_t *code;       /* L_max */
   NodeRec *node;       /* node_cap */
@@ -342,50 +430,84 @@ struct Arena {
   StoreRec *store;     /* store_cap */
   char *store_db;      /* store_cap * L */
   int32_t *nlist;      /* nlist_cap: node lists of stored structures */
-  uint64_t *seen_lo, *seen_hi; /* seen_cap */
+  int32_t *ncnt;       /* nlist_cap: candidates of that node passing for the owning structure */
+  SeenEnt *seen;       /* seen_cap; lo == 0 marks an empty slot (kept clean between runs) */
+  int32_t *seen_used;  /* seen_cap: occupied slots, for the clean-up */
   unsigned long long *nht;     /* nht_cap: (hash32 << 32) | (node id + 1), 0 = empty */
   NewRec *fresh;       /* new_cap */
-  uint64_t *keys;      /* new_cap + max_stack: sort keys / lag keys (>= 2*L_max) */
   int32_t *sel;        /* max_stack: selected entries of the next beam */
+  int32_t *sel_idx;    /* max_stack: the same before ranking */
+  int32_t *sel_store;  /* max_stack: selected rank -> store index */
   int32_t *beam;       /* max_stack: store indices */
   int32_t *traj_n;     /* step_cap */
   int32_t *traj;       /* step_cap * max_stack: store indices */
   int32_t *todo;       /* todo_cap * 3 */
   int32_t *todo_id;    /* todo_cap */
-  /* node expansion scratch */
-  uint16_t *pos;       /* L_max */
-  uint16_t *brcnt;     /* L_max + 1 */
-  uint8_t *ncode;      /* L_max */
-  int32_t *ranked;     /* nb_mode */
-  int32_t *tmp_dE;     /* nb_mode */
-  uint32_t *tmp_stem;  /* nb_mode * 2: (mip, mjp) and nb */
-  uint64_t *tmp_fp;    /* nb_mode * 2 */
-  int32_t *act_v, *act_c; /* L_max: nodes of the current structure that have candidates */
-  int32_t *flag, *pref, *ch_e; /* per-chunk: unseen flag, exclusive prefix, energy (blockDim) */
-  uint64_t *ch_lo, *ch_hi;     /* per-chunk fingerprints */
+  int32_t *flag, *pref; /* sel_cap = max(chunk_cap, new_cap + max_stack) */
+  int32_t *ch_e;       /* chunk_cap */
+  uint64_t *ch_lo, *ch_hi; /* chunk_cap */
+  char *wscratch;      /* nwarps * wscratch_bytes: node expansion scratch, one per warp */
+};
+
+/* Scratch of one node expansion (views into the warp's slice of Arena::wscratch). */
+struct WarpScratch {
+  uint64_t *keys;   /* key_cap: lag keys, later candidate keys */
+  uint16_t *pos;    /* L_max: local index -> original position */
+  uint16_t *brcnt;  /* L_max: branches of the loop before that position */
+  uint32_t *mask;   /* 10 * mask_words: F[A,C,G,U], R[A,C,G,U] (reversed), CL, CLR */
+  int32_t *ranked;  /* nb_mode: lag of rank r */
+  int32_t *r_dE;    /* nb_mode */
+  uint32_t *r_stem; /* nb_mode: (max_i << 16) | max_j */
+  int32_t *r_nb;    /* nb_mode */
+  int32_t *tmp;     /* 8 ints */
 };
 
 struct BlockShared {
   int32_t seq_index, L, status;
   int32_t n_node, n_pool16, n_cand, n_store, n_nlist, n_seen, n_todo, n_expand;
   int32_t beam_n, n_new, nb_branch, n_steps, n_traj;
-  int32_t tmp0, tmp1, tmp2;
-  int64_t cnt[CNT_N];
+  int32_t tmp0, tmp1, tmp2, cur_b, xcut;
+  int32_t emin, emax, cnt_le;
+  int32_t wsum[12];
+  unsigned long long cnt[CNT_N];
 };
 
 RF_HD size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+RF_HD int imax(int a, int b) { return a > b ? a : b; }
+
+/* sizes of the per-warp scratch pieces, in the order of WarpScratch */
+RF_HD size_t wscratch_carve(WarpScratch &W, char *base, const Caps &c, const FoldParams &fp) {
+  size_t off = 0;
+  int nrank = fp.nb_mode > 0 ? fp.nb_mode : 1;
+#define RF_WCARVE(field, type, count)                \
+  off = align_up(off, 16);                           \
+  W.field = (type *)(base ? base + off : nullptr);   \
+  off += sizeof(type) * (size_t)(count);
+  RF_WCARVE(keys, uint64_t, c.key_cap);
+  RF_WCARVE(pos, uint16_t, c.L_max);
+  RF_WCARVE(brcnt, uint16_t, c.L_max);
+  RF_WCARVE(mask, uint32_t, 10 * (size_t)c.mask_words);
+  RF_WCARVE(ranked, int32_t, nrank);
+  RF_WCARVE(r_dE, int32_t, nrank);
+  RF_WCARVE(r_stem, uint32_t, nrank);
+  RF_WCARVE(r_nb, int32_t, nrank);
+  RF_WCARVE(tmp, int32_t, 8);
+#undef RF_WCARVE
+  return align_up(off, 128);
+}
 
 /* Carve the arena; with base == nullptr just computes the size.  Returns bytes used. */
-RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &fp, int nthreads) {
+RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &fp) {
   size_t off = 0;
 #define RF_CARVE(field, type, count)                              \
   off = align_up(off, 16);                                        \
   A.field = (type *)(base ? base + off : nullptr);                \
   off += sizeof(type) * (size_t)(count);
   int L = c.L_max;
-  int nkeys = c.new_cap + fp.max_stack;
-  if (nkeys < 2 * L) nkeys = 2 * L;
-  int nrank = fp.nb_mode > 0 ? fp.nb_mode : 1;
+  int sel_cap = imax(c.chunk_cap, c.new_cap + fp.max_stack);
+  /* the two hash tables first: they are the part that must be zero before a run */
+  RF_CARVE(seen, SeenEnt, c.seen_cap);
+  RF_CARVE(nht, unsigned long long, c.nht_cap);
   RF_CARVE(code, uint8_t, L);
   RF_CARVE(node, NodeRec, c.node_cap);
   RF_CARVE(pool16, int16_t, c.pool16_cap);
@@ -393,33 +515,30 @@ RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &
   RF_CARVE(store, StoreRec, c.store_cap);
   RF_CARVE(store_db, char, (size_t)c.store_cap * L);
   RF_CARVE(nlist, int32_t, c.nlist_cap);
-  RF_CARVE(seen_lo, uint64_t, c.seen_cap);
-  RF_CARVE(seen_hi, uint64_t, c.seen_cap);
-  RF_CARVE(nht, unsigned long long, c.nht_cap);
+  RF_CARVE(ncnt, int32_t, c.nlist_cap);
+  RF_CARVE(seen_used, int32_t, c.seen_cap);
   RF_CARVE(fresh, NewRec, c.new_cap);
-  RF_CARVE(keys, uint64_t, nkeys);
   RF_CARVE(sel, int32_t, fp.max_stack);
+  RF_CARVE(sel_idx, int32_t, fp.max_stack);
+  RF_CARVE(sel_store, int32_t, fp.max_stack);
   RF_CARVE(beam, int32_t, fp.max_stack);
   RF_CARVE(traj_n, int32_t, c.step_cap);
   RF_CARVE(traj, int32_t, (size_t)c.step_cap * fp.max_stack);
   RF_CARVE(todo, int32_t, (size_t)c.todo_cap * 3);
   RF_CARVE(todo_id, int32_t, c.todo_cap);
-  RF_CARVE(pos, uint16_t, L);
-  RF_CARVE(brcnt, uint16_t, L + 1);
-  RF_CARVE(ncode, uint8_t, L);
-  RF_CARVE(ranked, int32_t, nrank);
-  RF_CARVE(tmp_dE, int32_t, nrank);
-  RF_CARVE(tmp_stem, uint32_t, (size_t)nrank * 2);
-  RF_CARVE(tmp_fp, uint64_t, (size_t)nrank * 2);
-  RF_CARVE(act_v, int32_t, L);
-  RF_CARVE(act_c, int32_t, L);
-  RF_CARVE(flag, int32_t, nthreads + 1);
-  RF_CARVE(pref, int32_t, nthreads + 1);
-  RF_CARVE(ch_e, int32_t, nthreads + 1);
-  RF_CARVE(ch_lo, uint64_t, nthreads + 1);
-  RF_CARVE(ch_hi, uint64_t, nthreads + 1);
+  RF_CARVE(flag, int32_t, sel_cap);
+  RF_CARVE(pref, int32_t, sel_cap);
+  RF_CARVE(ch_e, int32_t, c.chunk_cap);
+  RF_CARVE(ch_lo, uint64_t, c.chunk_cap);
+  RF_CARVE(ch_hi, uint64_t, c.chunk_cap);
+  off = align_up(off, 128);
+  RF_CARVE(wscratch, char, (size_t)c.nwarps * c.wscratch_bytes);
 #undef RF_CARVE
   return align_up(off, 256);
+}
+/* bytes at the start of an arena that hold the hash tables (zeroed by the host once) */
+RF_HD size_t arena_table_bytes(const Caps &c) {
+  return align_up(sizeof(SeenEnt) * (size_t)c.seen_cap, 16) + sizeof(unsigned long long) * (size_t)c.nht_cap;
 }
 
 /* ------------------------------------------------------------------------------------ */
@@ -466,6 +585,7 @@ struct Fold {
   /* candidates of node v are sorted by dE: count the leading ones that pass for energy e */
   RF_FN int count_pass(const NodeRec &n, int e_cur) const {
     int lo = 0, hi = n.cand_n; /* first index that fails */
+    if (prm.min_nrj == 0.0) return hi; /* every kept candidate has dE < 0 */
     while (lo < hi) {
       int mid = (lo + hi) >> 1;
       if (passes(e_cur, A.cand[n.cand_off + mid].dE)) lo = mid + 1; else hi = mid;
@@ -474,14 +594,17 @@ struct Fold {
   }
 
   RF_FN void fail(int code) {
-    /* called inside single phases or by any thread: status only ever goes 0 -> code */
+    /* called by any thread: status only ever goes 0 -> code */
     sh->status = code;
+  }
+  RF_FN void count(int which, long long v) {
+    Exec::atomic_add64(&sh->cnt[which], (unsigned long long)v);
   }
 
   /* --- node creation --------------------------------------------------------------------
    * Fill node record `id` for the loop closed by (ci,cj) with branches copied from parent
    * ranges.  Returns false on pool overflow. */
-  RF_FN bool build_node(int id, int ci, int cj, const NodeRec *par, int lo1, int hi1, int xp, int xq,
+  RF_NOINLINE bool build_node(int id, int ci, int cj, const NodeRec *par, int lo1, int hi1, int xp, int xq,
                         int lo2, int hi2, int lv) {
     int m = (hi1 - lo1) + (xp >= 0 ? 1 : 0) + (hi2 - lo2);
     int need = 2 * m + m + 2;
@@ -508,6 +631,7 @@ struct Fold {
     NodeRec &n = A.node[id];
     n.ci = ci; n.cj = cj; n.pool_off = off; n.br_n = m; n.lv = lv;
     n.cand_off = 0; n.cand_n = -1; n.n_ranked = 0; n.n_pos = 0; n.w_scan = 0; n.hash = h;
+    n.nht_slot = -1;
     n.e_loop = loop_energy(ev, ci, cj, br, 0, m, -1, -1, 0, 0, lv);
     /* acc must equal lv: the node holds ALL unpaired positions of its loop */
     if (acc != lv) return false;
@@ -521,8 +645,8 @@ struct Fold {
     return true;
   }
   /* Insert node `id` into the unique-loop table or find the identical loop already there. */
-  RF_FN int nht_resolve(int id) {
-    const NodeRec &n = A.node[id];
+  RF_NOINLINE int nht_resolve(int id) {
+    NodeRec &n = A.node[id];
     unsigned long long tag = ((n.hash >> 32) << 32) | (unsigned)(id + 1);
     unsigned mask = caps.nht_cap - 1;
     unsigned slot = (unsigned)n.hash & mask;
@@ -530,7 +654,7 @@ struct Fold {
       unsigned long long cur = A.nht[slot];
       if (cur == 0) {
         cur = Exec::atomic_cas64(&A.nht[slot], 0ULL, tag);
-        if (cur == 0) return id;
+        if (cur == 0) { n.nht_slot = (int32_t)slot; return id; }
       }
       if ((cur >> 32) == (tag >> 32)) {
         int other = (int)(cur & 0xffffffffu) - 1;
@@ -541,143 +665,219 @@ struct Fold {
     return -1; /* table full */
   }
 
+  /* --- warp-scope bitonic sort of n (power of two) 64-bit keys ---------------------------- */
+  RF_NOINLINE void wsort(uint64_t *keys, int n, bool descending) {
+    for (int k = 2; k <= n; k <<= 1) {
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        RF_WPAR_BEGIN(t, n >> 1)
+          int i = ((t & ~(j - 1)) << 1) | (t & (j - 1)); /* lower index of the pair */
+          int l = i | j;
+          uint64_t a = keys[i], b = keys[l];
+          bool up = ((i & k) == 0) != descending; /* ascending run? */
+          if ((a > b) == up) { keys[i] = b; keys[l] = a; }
+        RF_WPAR_END
+      }
+    }
+  }
+
   /* --- node expansion: correlation -> top-n lags -> stem scan -> energy change ------------
    * Everything create_childs/find_best_consecutives compute for one unpaired region
-   * (rafft.py:112-123, 86-109), done once per unique loop. */
-  RF_NOINLINE void expand_node(int v) {
+   * (rafft.py:112-123, 86-109), done once per unique loop, by ONE warp (warp-scope phases).
+   *
+   * The region x[0..lv) is held as one-hot bit masks F_X (bit i = [x_i == X]) and their
+   * reversals R_X (bit k = [x_{lv-1-k} == X]).  For lag p the partner of i is j = p - i, i.e.
+   * reversed index k = i + s with s = lv-1-p, so "x_i = X pairs x_j = Y" for 32 positions at a
+   * time is F_X & (R_Y >> s): the correlation is three popcounts per word, the stem scan
+   * walks the set bits of the pairable mask. */
+  RF_FN unsigned mword(const uint32_t *M, int a, int nw) const { return (a >= 0 && a < nw) ? M[a] : 0u; }
+  /* bits [32*wi + s, 32*wi + s + 32) of mask M (nw words), any integer s */
+  RF_FN unsigned mshift(const uint32_t *M, int wi, int s, int nw) const {
+    int q = 32 * wi + s;
+    int a = q >> 5, b = q & 31; /* arithmetic shift = floor */
+    return Exec::funnel_r(mword(M, a, nw), mword(M, a + 1, nw), b);
+  }
+
+  RF_NOINLINE void expand_node(int v, int wslot) {
     NodeRec &n = A.node[v];
     const int lv = n.lv, m = n.br_n;
     const int nlag = 2 * lv - 1;
-    /* 1. local index -> original position / branch count / base code */
-    RF_PAR_BEGIN(t, lv)
+    const int nw = (lv + 31) >> 5, MW = caps.mask_words;
+    WarpScratch W;
+    wscratch_carve(W, A.wscratch + (size_t)wslot * (size_t)caps.wscratch_bytes, caps, prm);
+    uint32_t *const F = W.mask, *const R = W.mask + 4 * MW, *const CL = W.mask + 8 * MW,
+                   *const CLR = W.mask + 9 * MW;
+    const uint8_t *const code = A.code;
+    /* 1. local index -> original position / branch count; one-hot masks; contiguity masks
+     *    (CL bit t: position t continues position t-1 in ORIGINAL coordinates) */
+    RF_WPAR_BEGIN(x, 10 * MW)
+      W.mask[x] = 0;
+    RF_WPAR_END
+    RF_WPAR_BEGIN(x, 8)
+      W.tmp[x] = 0;
+    RF_WPAR_END
+    RF_WPAR_BEGIN(t, lv)
       int k = seg_of(n, t);
-      int p = seg_start(n, k) + (t - node_segoff(n)[k]);
-      A.pos[t] = (uint16_t)p;
-      A.brcnt[t] = (uint16_t)k;
-      A.ncode[t] = A.code[p];
-    RF_PAR_END
+      int first = node_segoff(n)[k];
+      int p = seg_start(n, k) + (t - first);
+      W.pos[t] = (uint16_t)p;
+      W.brcnt[t] = (uint16_t)k;
+      int c = code[p], u = lv - 1 - t;
+      Exec::atomic_or(&F[c * MW + (t >> 5)], 1u << (t & 31));
+      Exec::atomic_or(&R[c * MW + (u >> 5)], 1u << (u & 31));
+      if (t > first) {
+        Exec::atomic_or(&CL[t >> 5], 1u << (t & 31));
+        Exec::atomic_or(&CLR[u >> 5], 1u << (u & 31));
+      }
+    RF_WPAR_END
     /* 2. pair-weighted correlation of the region against its reverse (utils.py:115-132):
-     *    cor[p] = sum_{i+j=p} w(s_i,s_j) = 2 * (half anti-diagonal), exact integers;
+     *    cor[p] = sum_{i+j=p} w(s_i,s_j) = 2 * sum over unordered pairs, exact integers;
      *    c[p] = cor[p] / (min(p, 2lv-2-p) + 1.0) as the reference's float64.
      *    key = order-preserving bits of c[p] with the lag in the low bits, so that sorting
      *    keys descending is the reference's (value desc, lag desc) order (rafft.py:118,92). */
-    RF_PAR_BEGIN(p, nlag)
-      int i0 = p < lv ? 0 : p - lv + 1;
-      int d = p < lv ? p + 1 : 2 * lv - 1 - p;
-      int half = d >> 1;
-      int acc = 0;
-      for (int t = 0; t < half; t++) acc += prm.wi[A.ncode[i0 + t]][A.ncode[p - i0 - t]];
-      double cor = Exec::ddiv((double)(2 * (int64_t)acc), 16.0);
-      double norm = (double)(p < lv ? p : 2 * lv - 2 - p) + 1.0;
-      double c = Exec::ddiv(cor, norm);
-      A.keys[p] = (Exec::dbits(c) & ~0x1FFFULL) | (uint64_t)p;
-    RF_PAR_END
-    /* 3. rank by counting; the first nb_mode lags in order */
+    int nk = 32;
+    while (nk < nlag) nk <<= 1;
+    const int wGC = prm.wi[1][2], wAU = prm.wi[0][3], wGU = prm.wi[2][3];
+    RF_WPAR_BEGIN(p, nk)
+      uint64_t key = 0;
+      if (p < nlag) {
+        const int s = lv - 1 - p;
+        const int i0 = p < lv ? 0 : p - lv + 1, i1 = p < lv ? p : lv - 1;
+        int acc = 0;
+        for (int wi = i0 >> 5; wi <= (i1 >> 5); wi++) {
+          unsigned fg = F[2 * MW + wi], fa = F[0 * MW + wi];
+          unsigned rc = mshift(R + 1 * MW, wi, s, nw), ru = mshift(R + 3 * MW, wi, s, nw);
+          acc += wGC * Exec::popc(fg & rc) + wAU * Exec::popc(fa & ru) + wGU * Exec::popc(fg & ru);
+        }
+        double cor = Exec::ddiv((double)(2 * (int64_t)acc), 16.0);
+        double norm = (double)(p < lv ? p : 2 * lv - 2 - p) + 1.0;
+        double c = Exec::ddiv(cor, norm);
+        key = (Exec::dbits(c) & ~0x1FFFULL) | (uint64_t)p;
+      }
+      W.keys[p] = key;
+    RF_WPAR_END
+    /* 3. rank: the first nb_mode lags in (value desc, lag desc) order */
+    wsort(W.keys, nk, true);
     const int nr = nlag < prm.nb_mode ? nlag : prm.nb_mode;
-    RF_PAR_BEGIN(p, nlag)
-      uint64_t key = A.keys[p];
-      int r = 0;
-      for (int q = 0; q < nlag; q++) r += A.keys[q] > key;
-      if (r < nr) A.ranked[r] = p;
-    RF_PAR_END
-    /* 4. per ranked lag: longest-scoring consecutive stem (window_slide, rafft.py:36-83)
-     *    and the energy change of forming it (eval_one_struct difference, rafft.py:98). */
-    RF_PAR_BEGIN(r, nr)
-      const int p = A.ranked[r];
+    RF_WPAR_BEGIN(r, nr)
+      W.ranked[r] = (int)(W.keys[r] & 0x1FFFULL);
+    RF_WPAR_END
+    /* 4. per ranked lag: best-scoring consecutive stem (window_slide, rafft.py:36-83), walking
+     *    only the positions whose pair weight is non-zero, and the energy change of forming
+     *    it (eval_one_struct difference, rafft.py:98). */
+    const double dGC = prm.w[1][2], dAU = prm.w[0][3], dGU = prm.w[2][3];
+    RF_WPAR_BEGIN(r, nr)
+      const int p = W.ranked[r];
+      const int s = lv - 1 - p;
       const int i0 = p < lv ? 0 : p - lv + 1;
       const int d = p < lv ? p + 1 : 2 * lv - 1 - p;
       const int len2 = (d >> 1) + (d & 1);
-      int max_nb = 0, tmp_max = 0, max_i = 0, max_j = 0;
+      const int iend = i0 + len2; /* exclusive */
+      int max_nb = 0, tmp_max = 0, max_i = 0, max_j = 0, last_i = -2;
       double max_score = 0.0, prev = 0.0;
-      for (int t = 0; t < len2; t++) {
-        int ip = i0 + t, jp = p - i0 - t;
-        double tot = prm.w[A.ncode[ip]][A.ncode[jp]];
-        if (t > 0 && A.pos[ip] - A.pos[ip - 1] == 1 && A.pos[jp + 1] - A.pos[jp] == 1)
-          tot = Exec::dmul(Exec::dadd(prev, tot), tot);
-        if (tot == 0.0) tmp_max = 0; else tmp_max++;
-        if (tot >= max_score && (int)A.pos[jp] - (int)A.pos[ip] > prm.min_hp) {
-          max_score = tot; max_nb = tmp_max; max_i = ip; max_j = jp;
+      for (int wi = i0 >> 5; wi <= ((iend - 1) >> 5); wi++) {
+        unsigned fa = F[0 * MW + wi], fc = F[1 * MW + wi], fg = F[2 * MW + wi], fu = F[3 * MW + wi];
+        unsigned ra = mshift(R + 0 * MW, wi, s, nw), rc = mshift(R + 1 * MW, wi, s, nw),
+                 rg = mshift(R + 2 * MW, wi, s, nw), ru = mshift(R + 3 * MW, wi, s, nw);
+        unsigned gc = (fg & rc) | (fc & rg), au = (fa & ru) | (fu & ra), gu = (fg & ru) | (fu & rg);
+        if (dGC == 0.0) gc = 0;
+        if (dAU == 0.0) au = 0;
+        if (dGU == 0.0) gu = 0;
+        unsigned range = 0xffffffffu;
+        if (32 * wi < i0) range &= 0xffffffffu << (i0 - 32 * wi);
+        if (32 * wi + 32 > iend) range &= 0xffffffffu >> (32 * wi + 32 - iend);
+        unsigned P = (gc | au | gu) & range;
+        /* in-segment: both arms continue in original coordinates (rafft.py:67), t > 0 */
+        unsigned IS = CL[wi] & mshift(CLR, wi, s - 1, nw);
+        if ((i0 >> 5) == wi) IS &= ~(1u << (i0 & 31));
+        while (P) {
+          const int b = Exec::ffs(P) - 1;
+          P &= P - 1;
+          const int i = 32 * wi + b;
+          const double w = ((gc >> b) & 1) ? dGC : ((au >> b) & 1) ? dAU : dGU;
+          const bool adjacent = last_i == i - 1;
+          double tot = w;
+          if ((IS >> b) & 1) tot = Exec::dmul(Exec::dadd(adjacent ? prev : 0.0, w), w);
+          tmp_max = adjacent ? tmp_max + 1 : 1;
+          if (tot >= max_score && (int)W.pos[p - i] - (int)W.pos[i] > prm.min_hp) {
+            max_score = tot; max_nb = tmp_max; max_i = i; max_j = p - i;
+          }
+          prev = tot;
+          last_i = i;
         }
-        prev = tot;
       }
       int dE = 0x7fffffff;
-      uint64_t flo = 0, fhi = 0;
       if (max_nb > 0) {
         const int16_t *br = node_br(n);
         int e = 0;
         /* loop closed by the innermost pair: the region's branches between its two arms */
-        int a0 = A.pos[max_i], b0 = A.pos[max_j];
-        e += loop_energy(ev, a0, b0, br, A.brcnt[max_i] , A.brcnt[max_j], -1, -1, 0, 0,
+        int a0 = W.pos[max_i], b0 = W.pos[max_j];
+        e += loop_energy(ev, a0, b0, br, W.brcnt[max_i], W.brcnt[max_j], -1, -1, 0, 0,
                          max_j - max_i - 1);
         /* loops between consecutive pairs of the stem (stack, or a junction if the stem
          * steps over existing helices: contiguity breaks do not end a stem, rafft.py:71-74) */
         int ak = a0, bk = b0;
-        for (int k = 0; k < max_nb; k++) {
-          uint64_t l1, h1;
-          pair_fp(ak, bk, l1, h1);
-          flo += l1; fhi += h1;
-          if (k + 1 < max_nb) {
-            int an = A.pos[max_i - k - 1], bn = A.pos[max_j + k + 1];
-            e += loop_energy(ev, an, bn, br, A.brcnt[max_i - k - 1], A.brcnt[max_i - k], ak, bk,
-                             A.brcnt[max_j + k], A.brcnt[max_j + k + 1], 0);
-            ak = an; bk = bn;
-          }
+        for (int k = 0; k + 1 < max_nb; k++) {
+          int an = W.pos[max_i - k - 1], bn = W.pos[max_j + k + 1];
+          e += loop_energy(ev, an, bn, br, W.brcnt[max_i - k - 1], W.brcnt[max_i - k], ak, bk,
+                           W.brcnt[max_j + k], W.brcnt[max_j + k + 1], 0);
+          ak = an; bk = bn;
         }
         /* the region's own loop with the stem as a new branch */
         int io = max_i - max_nb + 1, jo = max_j + max_nb - 1;
-        e += loop_energy(ev, n.ci, n.cj, br, 0, A.brcnt[io], ak, bk, A.brcnt[jo], m,
+        e += loop_energy(ev, n.ci, n.cj, br, 0, W.brcnt[io], ak, bk, W.brcnt[jo], m,
                          io + (lv - 1 - jo));
         dE = e - n.e_loop;
       }
-      A.tmp_dE[r] = dE;
-      A.tmp_stem[2 * r] = ((uint32_t)max_i << 16) | (uint32_t)max_j;
-      A.tmp_stem[2 * r + 1] = (uint32_t)max_nb;
-      A.tmp_fp[2 * r] = flo;
-      A.tmp_fp[2 * r + 1] = fhi;
-    RF_PAR_END
-    /* 5. keep stems with dE below the threshold, stably sorted by dE (rafft.py:108) */
-    RF_SINGLE_BEGIN
-      int keep = 0, npos = 0;
-      int64_t ws = 0;
-      for (int r = 0; r < nr; r++) {
-        int p = A.ranked[r];
-        int d = p < lv ? p + 1 : 2 * lv - 1 - p;
-        ws += (d >> 1) + (d & 1);
-        if (A.tmp_stem[2 * r + 1] > 0) npos++;
-        if (A.tmp_stem[2 * r + 1] > 0 && A.tmp_dE[r] < prm.cand_thr) keep++;
-      }
-      n.n_ranked = nr; n.n_pos = npos; n.w_scan = ws;
-      int off = sh->n_cand;
-      if (off + keep > caps.cand_cap) { fail(ST_ERR_CAPACITY); keep = 0; }
-      sh->n_cand = off + keep;
-      n.cand_off = off;
-      sh->tmp0 = keep;
-      sh->cnt[CNT_UNIQ_NODES] += 1;
-      sh->cnt[CNT_UNIQ_W_CORR] += (int64_t)lv * (lv + 1) / 2;
-      sh->cnt[CNT_UNIQ_W_SCAN] += ws;
-    RF_SINGLE_END
-    const int keep = sh->tmp0;
-    RF_PAR_BEGIN(r, nr)
-      if (keep > 0 && A.tmp_stem[2 * r + 1] > 0 && A.tmp_dE[r] < prm.cand_thr) {
-        int dE = A.tmp_dE[r], at = 0;
-        for (int q = 0; q < nr; q++)
-          if (A.tmp_stem[2 * q + 1] > 0 && A.tmp_dE[q] < prm.cand_thr &&
-              (A.tmp_dE[q] < dE || (A.tmp_dE[q] == dE && q < r)))
-            at++;
-        Cand &c = A.cand[n.cand_off + at];
-        uint32_t ij = A.tmp_stem[2 * r];
-        int mip = ij >> 16, mjp = ij & 0xffff, nb = (int)A.tmp_stem[2 * r + 1];
-        c.dE = dE; c.mip = (uint16_t)mip; c.mjp = (uint16_t)mjp; c.nb = (uint16_t)nb;
+      W.r_dE[r] = dE;
+      W.r_stem[r] = ((uint32_t)max_i << 16) | (uint32_t)max_j;
+      W.r_nb[r] = max_nb;
+      /* 5. stems below the threshold get a (dE, rank) key: stable order by dE (rafft.py:108) */
+      const bool kept = max_nb > 0 && dE < prm.cand_thr;
+      W.keys[r] = kept ? (((uint64_t)(uint32_t)(dE ^ 0x80000000)) << 32) | (uint32_t)r : ~0ULL;
+      Exec::atomic_add(&W.tmp[0], len2);
+      if (max_nb > 0) Exec::atomic_add(&W.tmp[1], 1);
+      if (kept) Exec::atomic_add(&W.tmp[2], 1);
+    RF_WPAR_END
+    int nrp = 32;
+    while (nrp < nr) nrp <<= 1;
+    RF_WPAR_BEGIN(r, nrp - nr)
+      W.keys[nr + r] = ~0ULL;
+    RF_WPAR_END
+    const int keep_n = W.tmp[2];
+    if (keep_n > 0) wsort(W.keys, nrp, false);
+    RF_WSINGLE_BEGIN
+      n.n_ranked = nr; n.n_pos = W.tmp[1]; n.w_scan = W.tmp[0];
+      int off = Exec::atomic_add(&sh->n_cand, keep_n);
+      if (off + keep_n > caps.cand_cap) { fail(ST_ERR_CAPACITY); off = -1; }
+      W.tmp[3] = off;
+      count(CNT_UNIQ_NODES, 1);
+      count(CNT_UNIQ_W_CORR, (long long)lv * (lv + 1) / 2);
+      count(CNT_UNIQ_W_SCAN, W.tmp[0]);
+    RF_WSINGLE_END
+    const int off = W.tmp[3];
+    if (off >= 0) {
+      RF_WPAR_BEGIN(at, keep_n)
+        const int r = (int)(W.keys[at] & 0xffffffffu);
+        Cand &c = A.cand[off + at];
+        const uint32_t ij = W.r_stem[r];
+        const int mip = ij >> 16, mjp = ij & 0xffff, nb = W.r_nb[r];
+        c.dE = W.r_dE[r]; c.mip = (uint16_t)mip; c.mjp = (uint16_t)mjp; c.nb = (uint16_t)nb;
         c.rank = (uint16_t)r;
         c.inner_id = (mjp - mip > 1) ? -1 : -2;                       /* rafft.py:130 */
         c.outer_id = (mip - (nb - 1) > 0 || mjp + nb < lv) ? -1 : -2; /* rafft.py:141 */
-        c.fp_lo = A.tmp_fp[2 * r];
-        c.fp_hi = A.tmp_fp[2 * r + 1];
-      }
-    RF_PAR_END
-    RF_SINGLE_BEGIN
-      n.cand_n = keep;
-    RF_SINGLE_END
+        uint64_t flo = 0, fhi = 0;
+        for (int k = 0; k < nb; k++) {
+          uint64_t l1, h1;
+          pair_fp(W.pos[mip - k], W.pos[mjp + k], l1, h1);
+          flo += l1; fhi += h1;
+        }
+        c.fp_lo = flo; c.fp_hi = fhi;
+      RF_WPAR_END
+    }
+    RF_WSINGLE_BEGIN
+      n.cand_off = off < 0 ? 0 : off;
+      n.cand_n = off < 0 ? 0 : keep_n;
+    RF_WSINGLE_END
   }
 
   /* --- seen set (global per sequence, rafft.py:196-200) ------------------------------- */
@@ -685,9 +885,9 @@ struct Fold {
     unsigned mask = caps.seen_cap - 1;
     unsigned slot = (unsigned)(lo ^ (hi >> 7)) & mask;
     for (;;) {
-      uint64_t l = A.seen_lo[slot];
+      uint64_t l = A.seen[slot].lo;
       if (l == 0) return false;
-      if (l == lo && A.seen_hi[slot] == hi) return true;
+      if (l == lo && A.seen[slot].hi == hi) return true;
       slot = (slot + 1) & mask;
     }
   }
@@ -695,24 +895,26 @@ struct Fold {
     unsigned mask = caps.seen_cap - 1;
     unsigned slot = (unsigned)(lo ^ (hi >> 7)) & mask;
     for (;;) {
-      if (A.seen_lo[slot] == 0 &&
-          Exec::atomic_cas64((unsigned long long *)&A.seen_lo[slot], 0ULL, lo) == 0ULL) {
-        A.seen_hi[slot] = hi;
+      if (A.seen[slot].lo == 0 &&
+          Exec::atomic_cas64((unsigned long long *)&A.seen[slot].lo, 0ULL, lo) == 0ULL) {
+        A.seen[slot].hi = hi;
+        A.seen_used[Exec::atomic_add(&sh->n_seen, 1)] = (int32_t)slot;
         return;
       }
       slot = (slot + 1) & mask;
     }
   }
 
-  /* decode combination index -> (energy, fingerprint) of the child of store entry S */
-  RF_FN void combo_eval(const StoreRec &S, int m, uint64_t combo, int &e, uint64_t &lo,
-                        uint64_t &hi) const {
+  /* decode combination index -> (energy, fingerprint) of the child of store entry S:
+   * itertools.product over the nodes that have candidates, last list varies fastest */
+  RF_FN void combo_eval(const StoreRec &S, uint64_t combo, int &e, uint64_t &lo, uint64_t &hi) const {
     e = S.e; lo = S.fp_lo; hi = S.fp_hi;
-    for (int k = m - 1; k >= 0; k--) { /* itertools.product: last list varies fastest */
-      uint32_t c = (uint32_t)A.act_c[k];
-      uint32_t dgt = (uint32_t)(combo % c);
-      combo /= c;
-      const Cand &cd = A.cand[A.node[A.act_v[k]].cand_off + dgt];
+    for (int k = S.nl_n - 1; k >= 0; k--) {
+      uint32_t c = (uint32_t)A.ncnt[S.nl_off + k];
+      if (c == 0) continue;
+      uint32_t dgt = c == 1 ? 0u : (uint32_t)(combo % c);
+      if (c != 1) combo /= c;
+      const Cand &cd = A.cand[A.node[A.nlist[S.nl_off + k]].cand_off + dgt];
       e += cd.dE; lo += cd.fp_lo; hi += cd.fp_hi;
     }
     if (lo == 0) lo = 1; /* 0 marks an empty slot of the seen table */
@@ -727,7 +929,7 @@ struct Fold {
       sh->n_seen = 0; sh->n_todo = 0; sh->n_expand = 0; sh->beam_n = 0; sh->n_new = 0;
       sh->nb_branch = 0; sh->n_steps = 0; sh->n_traj = 0;
       for (int k = 0; k < CNT_N; k++) sh->cnt[k] = 0;
-      sh->cnt[CNT_T0_NS] = Exec::now_ns();
+      sh->cnt[CNT_T0_NS] = (unsigned long long)Exec::now_ns();
       if (L > caps.L_max) sh->status = ST_ERR_CAPACITY;
       else if (L < 1) sh->status = ST_ERR_SEQ; /* the reference cannot fold an empty sequence */
     RF_SINGLE_END
@@ -737,15 +939,10 @@ struct Fold {
         int c = ch == 'A' ? 0 : ch == 'C' ? 1 : ch == 'G' ? 2 : ch == 'U' ? 3 : -1;
         if (c < 0) { sh->status = ST_ERR_SEQ; c = 0; }
         A.code[i] = (uint8_t)c;
+        A.store_db[i] = '.';
       RF_PAR_END
     }
     if (sh->status == ST_OK) {
-      RF_PAR_BEGIN(i, caps.seen_cap)
-        A.seen_lo[i] = 0;
-      RF_PAR_END
-      RF_PAR_BEGIN(i, caps.nht_cap)
-        A.nht[i] = 0;
-      RF_PAR_END
       ev.P = E; ev.s = A.code; ev.L = L;
       /* root: exterior loop without branches, completely unfolded structure (rafft.py:226-231) */
       RF_SINGLE_BEGIN
@@ -758,14 +955,20 @@ struct Fold {
         sh->n_nlist = 1; sh->n_store = 1;
         A.beam[0] = 0; sh->beam_n = 1;
       RF_SINGLE_END
-      RF_PAR_BEGIN(i, L)
-        A.store_db[i] = '.';
-      RF_PAR_END
       while (sh->status == ST_OK) {
         if (!step()) break;
       }
     }
     emit(out);
+    /* leave the two hash tables empty for the next sequence of this arena */
+    RF_PAR_BEGIN(i, sh->n_seen)
+      A.seen[A.seen_used[i]].lo = 0;
+      A.seen[A.seen_used[i]].hi = 0;
+    RF_PAR_END
+    RF_PAR_BEGIN(i, sh->n_node)
+      int s = A.node[i].nht_slot;
+      if (s >= 0) A.nht[s] = 0;
+    RF_PAR_END
   }
 
   /* One bfs_pairs call (rafft.py:156-216).  Returns false when the beam has converged. */
@@ -785,148 +988,245 @@ struct Fold {
     RF_SINGLE_END
     if (sh->status != ST_OK) return false;
 
-    /* ---- P1: expand the loops of the beam that have not been expanded yet */
-    for (int b = 0; b < beam_n; b++) {
+    /* ---- P1: expand the loops of the beam that have not been expanded yet, one warp each */
+    RF_PAR_BEGIN(b, beam_n)
       const StoreRec &S = A.store[A.beam[b]];
-      if (S.done) continue;
-      RF_PAR_BEGIN(k, S.nl_n)
-        int v = A.nlist[S.nl_off + k];
-        if (A.node[v].cand_n == -1 && Exec::atomic_cas(&A.node[v].cand_n, -1, -2) == -1) {
-          int at = Exec::atomic_add(&sh->n_expand, 1);
-          if (at < caps.todo_cap) A.todo_id[at] = v;
+      if (!S.done) {
+        for (int k = 0; k < S.nl_n; k++) {
+          int v = A.nlist[S.nl_off + k];
+          if (A.node[v].cand_n == -1 && Exec::atomic_cas(&A.node[v].cand_n, -1, -2) == -1) {
+            int at = Exec::atomic_add(&sh->n_expand, 1);
+            if (at < caps.todo_cap) A.todo_id[at] = v;
+          }
         }
-      RF_PAR_END
-    }
+      }
+    RF_PAR_END
     if (sh->n_expand > caps.todo_cap) { RF_SINGLE_BEGIN fail(ST_ERR_CAPACITY); RF_SINGLE_END return false; }
     {
       const int ne = sh->n_expand;
-      /* deterministic order (candidate pool layout) regardless of thread interleaving */
-      RF_SINGLE_BEGIN
-        for (int a = 1; a < ne; a++) {
-          int x = A.todo_id[a], c = a - 1;
-          while (c >= 0 && A.todo_id[c] > x) { A.todo_id[c + 1] = A.todo_id[c]; c--; }
-          A.todo_id[c + 1] = x;
-        }
-      RF_SINGLE_END
-      for (int a = 0; a < ne && sh->status == ST_OK; a++) expand_node(A.todo_id[a]);
+      for (int a = Exec::warp(); a < ne; a += Exec::nwarps()) expand_node(A.todo_id[a], Exec::warp());
+      Exec::sync();
     }
     if (sh->status != ST_OK) return false;
 
     /* ---- P2: combine stems of independent regions (rafft.py:176-203) */
-    RF_SINGLE_BEGIN
-      sh->n_new = 0; sh->nb_branch = 0;
-    RF_SINGLE_END
-    const int T = Exec::nthreads();
-    for (int b = 0; b < beam_n && sh->status == ST_OK; b++) {
+    /* P2a: per beam member, how many stems of each of its regions pass (rafft.py:102), the size
+     *      of its product, and the reference's work counters (create_childs runs for every
+     *      region of every beam member) */
+    RF_PAR_BEGIN(b, beam_n)
       StoreRec &S = A.store[A.beam[b]];
-      /* reference work counters: create_childs runs for every node of every beam member */
-      RF_SINGLE_BEGIN
-        int m = 0;
-        uint64_t prod = 1;
-        for (int k = 0; k < S.nl_n; k++) {
-          const NodeRec &nd = A.node[A.nlist[S.nl_off + k]];
-          sh->cnt[CNT_NODE_EXP] += 1;
-          sh->cnt[CNT_NODE_POS] += nd.lv;
-          sh->cnt[CNT_W_CORR] += (int64_t)nd.lv * (nd.lv + 1) / 2;
-          sh->cnt[CNT_W_SCAN] += nd.w_scan;
-          sh->cnt[CNT_N_EVAL] += nd.n_pos;
-          if (!S.done) {
-            int c = count_pass(nd, S.e);
-            if (c > 0) {
-              A.act_v[m] = A.nlist[S.nl_off + k];
-              A.act_c[m] = c;
-              m++;
-              prod = prod > (1ULL << 62) / (uint64_t)c ? (1ULL << 62) : prod * (uint64_t)c;
-            }
+      long long c_pos = 0, c_corr = 0, c_scan = 0, c_eval = 0;
+      int mact = 0;
+      uint64_t prod = 1;
+      for (int k = 0; k < S.nl_n; k++) {
+        const NodeRec &nd = A.node[A.nlist[S.nl_off + k]];
+        c_pos += nd.lv; c_corr += (long long)nd.lv * (nd.lv + 1) / 2; c_scan += nd.w_scan; c_eval += nd.n_pos;
+        if (!S.done) {
+          int c = count_pass(nd, S.e);
+          A.ncnt[S.nl_off + k] = c;
+          if (c > 0) {
+            mact++;
+            prod = prod > (1ULL << 62) / (uint64_t)c ? (1ULL << 62) : prod * (uint64_t)c;
           }
         }
-        if (!S.done) {
-          S.nact = m;
-          S.prod = m ? prod : 0;
-          if (m == 0) S.done = 1;
+      }
+      count(CNT_NODE_EXP, S.nl_n); count(CNT_NODE_POS, c_pos); count(CNT_W_CORR, c_corr);
+      count(CNT_W_SCAN, c_scan); count(CNT_N_EVAL, c_eval);
+      if (!S.done) {
+        S.nact = mact;
+        S.prod = mact ? prod : 0;
+        if (mact == 0) S.done = 1;
+      }
+    RF_PAR_END
+    RF_SINGLE_BEGIN
+      sh->n_new = 0; sh->nb_branch = 0; sh->cur_b = 0;
+    RF_SINGLE_END
+    /* P2b: members are enumerated one after the other while nb_branch < max_branch */
+    const int CH = caps.chunk_cap;
+    for (;;) {
+      RF_SINGLE_BEGIN
+        int b = sh->cur_b;
+        while (b < beam_n && sh->nb_branch < prm.max_branch) {
+          const StoreRec &S = A.store[A.beam[b]];
+          if (!S.done) break;
+          /* a member whose product was exhausted earlier: the reference walks it again
+           * (every child is already in `seen`), we only account for it */
+          sh->cnt[CNT_COMBOS] += S.prod; sh->cnt[CNT_N_EVAL] += S.prod;
+          b++;
         }
-        /* a member whose product was exhausted earlier: the reference walks it again
-         * (every child is already in `seen`), we only account for it */
-        if (S.done && S.prod) {
-          uint64_t walked = sh->nb_branch >= prm.max_branch ? 1 : S.prod;
-          sh->cnt[CNT_COMBOS] += walked;
-          sh->cnt[CNT_N_EVAL] += walked;
-        }
+        sh->cur_b = b;
       RF_SINGLE_END
-      if (S.done) continue;
-      const int m = (int)S.nact;
-      const uint64_t limit = sh->nb_branch >= prm.max_branch ? 1 : S.prod;
+      const int b = sh->cur_b;
+      if (b >= beam_n || sh->nb_branch >= prm.max_branch || sh->status != ST_OK) break;
+      StoreRec &S = A.store[A.beam[b]];
+      const uint64_t limit = S.prod;
       uint64_t processed = 0;
       bool cut = false;
       while (processed < limit && !cut && sh->status == ST_OK) {
-        const int chunk = (int)((limit - processed) < (uint64_t)T ? (limit - processed) : (uint64_t)T);
+        const int chunk = (int)((limit - processed) < (uint64_t)CH ? (limit - processed) : (uint64_t)CH);
         /* evaluate + look up (rafft.py:192-196); children of one structure are distinct */
         RF_PAR_BEGIN(i, chunk)
           int e_; uint64_t lo_, hi_;
-          combo_eval(S, m, processed + (uint64_t)i, e_, lo_, hi_);
+          combo_eval(S, processed + (uint64_t)i, e_, lo_, hi_);
           A.ch_e[i] = e_; A.ch_lo[i] = lo_; A.ch_hi[i] = hi_;
           A.flag[i] = !seen_has(lo_, hi_);
         RF_PAR_END
-        RF_SINGLE_BEGIN
-          /* exclusive prefix over the chunk + position of the max_branch cut: the reference
-           * breaks right after the combination that brings nb_branch to max_branch */
-          int run = 0, xcut = -1;
-          for (int i = 0; i < chunk && xcut < 0; i++) {
-            A.pref[i] = run;
-            run += A.flag[i];
-            if (sh->nb_branch + run >= prm.max_branch) xcut = i;
-          }
-          sh->tmp0 = xcut;
-          sh->tmp1 = run;               /* new children kept from this chunk */
-          sh->tmp2 = sh->n_new;         /* where they go */
-          if (sh->n_new + run > caps.new_cap) { fail(ST_ERR_CAPACITY); sh->tmp1 = 0; }
-        RF_SINGLE_END
-        const int xcut = sh->tmp0, base = sh->tmp2;
-        const int upto = xcut >= 0 ? xcut + 1 : chunk;
-        if (sh->status == ST_OK) {
-          RF_PAR_BEGIN(i, upto)
-            if (A.flag[i]) {
-              NewRec &r = A.fresh[base + A.pref[i]];
-              r.e = A.ch_e[i]; r.parent_slot = b; r.combo = processed + (uint64_t)i;
-              r.fp_lo = A.ch_lo[i]; r.fp_hi = A.ch_hi[i];
-              seen_put(A.ch_lo[i], A.ch_hi[i]);
-            }
-          RF_PAR_END
-          RF_SINGLE_BEGIN
-            sh->n_new += sh->tmp1;
-            sh->nb_branch += sh->tmp1;
-            sh->n_seen += sh->tmp1;
-            sh->cnt[CNT_COMBOS] += upto;
-            sh->cnt[CNT_N_EVAL] += upto;
-            if (2 * (sh->n_seen + prm.max_branch + prm.max_stack + T) > caps.seen_cap)
-              fail(ST_ERR_CAPACITY);
-          RF_SINGLE_END
+        const int nnew = Exec::scan_flags(A.flag, A.pref, chunk, sh->wsum);
+        /* the reference breaks right after the combination that brings nb_branch to
+         * max_branch: unseen children number nb0 .. of this chunk are kept up to that one */
+        const int nb0 = sh->nb_branch, base = sh->n_new;
+        const int room = prm.max_branch - nb0; /* > 0 */
+        const int take = nnew < room ? nnew : room;
+        if (base + take > caps.new_cap || 2 * (sh->n_seen + take) + 2 > caps.seen_cap) {
+          RF_SINGLE_BEGIN fail(ST_ERR_CAPACITY); RF_SINGLE_END
+          break;
         }
+        RF_SINGLE_BEGIN
+          sh->xcut = -1;
+        RF_SINGLE_END
+        RF_PAR_BEGIN(i, chunk)
+          if (A.flag[i] && A.pref[i] < take) {
+            NewRec &r = A.fresh[base + A.pref[i]];
+            r.e = A.ch_e[i]; r.parent_slot = b; r.combo = processed + (uint64_t)i;
+            r.fp_lo = A.ch_lo[i]; r.fp_hi = A.ch_hi[i];
+            seen_put(A.ch_lo[i], A.ch_hi[i]);
+            if (nnew >= room && A.pref[i] == take - 1) sh->xcut = i;
+          }
+        RF_PAR_END
+        const int xcut = sh->xcut;
+        const int upto = xcut >= 0 ? xcut + 1 : chunk;
+        RF_SINGLE_BEGIN
+          sh->n_new += take;
+          sh->nb_branch += take;
+          sh->cnt[CNT_COMBOS] += upto;
+          sh->cnt[CNT_N_EVAL] += upto;
+        RF_SINGLE_END
         processed += (uint64_t)upto;
         cut = xcut >= 0;
       }
-      if (processed == S.prod) {
+      RF_SINGLE_BEGIN
+        if (processed == S.prod) S.done = 1;
+        sh->cur_b = b + 1;
+      RF_SINGLE_END
+    }
+    if (sh->status != ST_OK) return false;
+    /* P2c: once nb_branch >= max_branch the `break` only leaves the product loop
+     *      (rafft.py:202-203): every later member still tries its first combination */
+    {
+      const int b0 = sh->cur_b;
+      const int rest = beam_n - b0;
+      if (rest > 0) {
+        RF_PAR_BEGIN(j, rest)
+          const StoreRec &S = A.store[A.beam[b0 + j]];
+          A.flag[j] = 0;
+          if (!S.done) {
+            int e_; uint64_t lo_, hi_;
+            combo_eval(S, 0, e_, lo_, hi_);
+            A.ch_e[j] = e_; A.ch_lo[j] = lo_; A.ch_hi[j] = hi_;
+            A.flag[j] = !seen_has(lo_, hi_);
+          }
+        RF_PAR_END
         RF_SINGLE_BEGIN
-          S.done = 1;
+          for (int j = 0; j < rest; j++) {
+            StoreRec &S = A.store[A.beam[b0 + j]];
+            if (S.done) {
+              if (S.prod) { sh->cnt[CNT_COMBOS] += 1; sh->cnt[CNT_N_EVAL] += 1; }
+              continue;
+            }
+            sh->cnt[CNT_COMBOS] += 1; sh->cnt[CNT_N_EVAL] += 1;
+            if (A.flag[j] && !seen_has(A.ch_lo[j], A.ch_hi[j])) {
+              if (sh->n_new + 1 > caps.new_cap || 2 * (sh->n_seen + 1) + 2 > caps.seen_cap) {
+                fail(ST_ERR_CAPACITY);
+                break;
+              }
+              NewRec &r = A.fresh[sh->n_new++];
+              r.e = A.ch_e[j]; r.parent_slot = b0 + j; r.combo = 0;
+              r.fp_lo = A.ch_lo[j]; r.fp_hi = A.ch_hi[j];
+              seen_put(A.ch_lo[j], A.ch_hi[j]);
+              sh->nb_branch++;
+            }
+            if (S.prod == 1) S.done = 1;
+          }
         RF_SINGLE_END
       }
     }
     if (sh->status != ST_OK) return false;
 
-    /* ---- P3: new + old, stable sort by energy, keep max_stack (rafft.py:206-210) */
+    /* ---- P3: new + old, stable sort by energy, keep max_stack (rafft.py:206-210).
+     *      Entry i < n_new is a new child (generation order), then the old beam in order;
+     *      the order is (energy, i).  Selection: bisect the energy threshold T of the
+     *      keep-th entry, take everything below T and the first entries equal to T. */
     const int n_new = sh->n_new;
     const int total = n_new + beam_n;
-    RF_PAR_BEGIN(i, total)
-      int e = i < n_new ? A.fresh[i].e : A.store[A.beam[i - n_new]].e;
-      A.keys[i] = ((uint64_t)(uint32_t)(e ^ 0x80000000)) << 32 | (uint32_t)i;
-    RF_PAR_END
     const int keep = total < prm.max_stack ? total : prm.max_stack;
-    RF_PAR_BEGIN(i, total)
-      uint64_t key = A.keys[i];
+#define RF_ENTRY_E(i) ((i) < n_new ? A.fresh[(i)].e : A.store[A.beam[(i) - n_new]].e)
+    if (total > keep) {
+      RF_SINGLE_BEGIN
+        sh->emin = 0x7fffffff; sh->emax = (int)0x80000000;
+      RF_SINGLE_END
+      {
+        int lo_ = 0x7fffffff, hi_ = (int)0x80000000, any = 0;
+        for (int i = Exec::tid(); i < total; i += Exec::stride()) {
+          int e = RF_ENTRY_E(i);
+          lo_ = e < lo_ ? e : lo_; hi_ = e > hi_ ? e : hi_; any = 1;
+        }
+        if (any) { Exec::atomic_min(&sh->emin, lo_); Exec::atomic_max(&sh->emax, hi_); }
+      }
+      Exec::sync();
+      long long blo = sh->emin, bhi = sh->emax; /* smallest T with count(e <= T) >= keep */
+      while (blo < bhi) {
+        const long long mid = (blo + bhi) >> 1; /* floor */
+        RF_SINGLE_BEGIN
+          sh->cnt_le = 0;
+        RF_SINGLE_END
+        int c = 0;
+        for (int i = Exec::tid(); i < total; i += Exec::stride()) c += RF_ENTRY_E(i) <= mid;
+        if (c) Exec::atomic_add(&sh->cnt_le, c);
+        Exec::sync();
+        if (sh->cnt_le >= keep) bhi = mid; else blo = mid + 1;
+      }
+      const int T_e = (int)blo;
+      RF_SINGLE_BEGIN
+        sh->cnt_le = 0;
+      RF_SINGLE_END
+      {
+        int c = 0;
+        for (int i = Exec::tid(); i < total; i += Exec::stride()) {
+          int e = RF_ENTRY_E(i);
+          c += e < T_e;
+          A.flag[i] = e == T_e;
+        }
+        if (c) Exec::atomic_add(&sh->cnt_le, c);
+      }
+      Exec::sync();
+      const int need_eq = keep - sh->cnt_le; /* >= 1 */
+      Exec::scan_flags(A.flag, A.pref, total, sh->wsum);
+      RF_PAR_BEGIN(i, total)
+        int e = RF_ENTRY_E(i);
+        A.flag[i] = (e < T_e) || (e == T_e && A.pref[i] < need_eq);
+      RF_PAR_END
+      Exec::scan_flags(A.flag, A.pref, total, sh->wsum);
+      RF_PAR_BEGIN(i, total)
+        if (A.flag[i]) A.sel_idx[A.pref[i]] = i;
+      RF_PAR_END
+    } else {
+      RF_PAR_BEGIN(i, total)
+        A.sel_idx[i] = i;
+      RF_PAR_END
+    }
+    /* rank the selected entries among themselves */
+    RF_PAR_BEGIN(x, keep)
+      const int i = A.sel_idx[x];
+      const int e = RF_ENTRY_E(i);
       int r = 0;
-      for (int q = 0; q < total; q++) r += A.keys[q] < key;
-      if (r < keep) A.sel[r] = i;
+      for (int y = 0; y < keep; y++) {
+        const int q = A.sel_idx[y];
+        const int eq = RF_ENTRY_E(q);
+        r += (eq < e) || (eq == e && q < i);
+      }
+      A.sel[r] = i;
     RF_PAR_END
+#undef RF_ENTRY_E
     /* same dot-bracket list => stop (rafft.py:213-214): new children are never equal to
      * old members (they were unseen), so the lists match iff no new child was selected */
     RF_SINGLE_BEGIN
@@ -942,7 +1242,6 @@ struct Fold {
     if (sh->status != ST_OK || sh->tmp0) return false;
 
     /* ---- P4: materialise the selected new children (dot-bracket, node list) */
-    const int store_base = sh->n_store;
     /* 4a. which child regions (inner / outer of the chosen stems) are not known yet */
     RF_PAR_BEGIN(r, keep)
       int i = A.sel[r];
@@ -953,10 +1252,10 @@ struct Fold {
         /* digits are produced last node first */
         int cnt_nodes = 0;
         for (int k = S.nl_n - 1; k >= 0; k--) {
+          int c = A.ncnt[S.nl_off + k];
+          if (c == 0) continue;
           int v = A.nlist[S.nl_off + k];
           const NodeRec &nd = A.node[v];
-          int c = count_pass(nd, S.e);
-          if (c == 0) continue;
           int dgt = (int)(combo % (uint64_t)c);
           combo /= (uint64_t)c;
           Cand &cd = A.cand[nd.cand_off + dgt];
@@ -972,7 +1271,7 @@ struct Fold {
             }
           }
         }
-        A.fresh[i].parent_slot |= cnt_nodes << 16; /* node count of the child, reused in 4d */
+        A.sel_store[r] = cnt_nodes; /* node count of the child, reused in 4d */
       }
     RF_PAR_END
     if (sh->n_todo > caps.todo_cap) { RF_SINGLE_BEGIN fail(ST_ERR_CAPACITY); RF_SINGLE_END return false; }
@@ -1016,14 +1315,13 @@ struct Fold {
       for (int r = 0; r < keep; r++) {
         int i = A.sel[r];
         if (i >= n_new) continue;
-        NewRec &nr = A.fresh[i];
-        int cnt_nodes = nr.parent_slot >> 16;
-        nr.parent_slot &= 0xffff;
+        const NewRec &nr = A.fresh[i];
+        int cnt_nodes = A.sel_store[r];
         StoreRec &C = A.store[at];
         C.e = nr.e; C.fp_lo = nr.fp_lo; C.fp_hi = nr.fp_hi; C.done = 0; C.prod = 0; C.nact = 0;
         C.nl_off = nl; C.nl_n = cnt_nodes;
         nl += cnt_nodes;
-        A.keys[r] = (uint64_t)at; /* selected rank -> store index */
+        A.sel_store[r] = at; /* selected rank -> store index */
         at++;
       }
       if (nl > caps.nlist_cap) fail(ST_ERR_CAPACITY);
@@ -1036,7 +1334,7 @@ struct Fold {
       int i = A.sel[r];
       if (i < n_new) {
         int parent = A.beam[A.fresh[i].parent_slot];
-        A.store_db[(size_t)A.keys[r] * L + pos] = A.store_db[(size_t)parent * L + pos];
+        A.store_db[(size_t)A.sel_store[r] * L + pos] = A.store_db[(size_t)parent * L + pos];
       }
     RF_PAR_END
     /* stems + node list */
@@ -1045,14 +1343,14 @@ struct Fold {
       if (i < n_new) {
         const NewRec &nr = A.fresh[i];
         const StoreRec &S = A.store[A.beam[nr.parent_slot]];
-        StoreRec &C = A.store[(int)A.keys[r]];
-        char *db = A.store_db + (size_t)A.keys[r] * L;
+        StoreRec &C = A.store[A.sel_store[r]];
+        char *db = A.store_db + (size_t)A.sel_store[r] * L;
         uint64_t combo = nr.combo;
         int w = C.nl_off + C.nl_n; /* filled backwards: nodes are visited last first */
         for (int k = S.nl_n - 1; k >= 0; k--) {
-          const NodeRec &nd = A.node[A.nlist[S.nl_off + k]];
-          int c = count_pass(nd, S.e);
+          int c = A.ncnt[S.nl_off + k];
           if (c == 0) continue;
+          const NodeRec &nd = A.node[A.nlist[S.nl_off + k]];
           int dgt = (int)(combo % (uint64_t)c);
           combo /= (uint64_t)c;
           const Cand &cd = A.cand[nd.cand_off + dgt];
@@ -1069,7 +1367,7 @@ struct Fold {
     RF_SINGLE_BEGIN
       for (int r = 0; r < keep; r++) {
         int i = A.sel[r];
-        A.sel[r] = i < n_new ? (int)A.keys[r] : A.beam[i - n_new];
+        A.sel[r] = i < n_new ? A.sel_store[r] : A.beam[i - n_new];
       }
       for (int r = 0; r < keep; r++) A.beam[r] = A.sel[r];
       sh->beam_n = keep;
@@ -1104,8 +1402,8 @@ struct Fold {
       out.seq_db[si] = (int64_t)d0;
       out.seq_step[si] = (int64_t)t0; out.seq_nstep[si] = nstep;
       out.seq_entry[si] = (int64_t)e0;
-      sh->cnt[CNT_T1_NS] = Exec::now_ns();
-      for (int k = 0; k < CNT_N; k++) out.counters[(size_t)si * CNT_N + k] = sh->cnt[k];
+      sh->cnt[CNT_T1_NS] = (unsigned long long)Exec::now_ns();
+      for (int k = 0; k < CNT_N; k++) out.counters[(size_t)si * CNT_N + k] = (int64_t)sh->cnt[k];
       sh->tmp0 = nstruct;
     RF_SINGLE_END
     const int nstruct = sh->tmp0;

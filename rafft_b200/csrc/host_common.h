@@ -133,25 +133,35 @@ inline int32_t pow2_at_least(int64_t x) {
   return (int32_t)p;
 }
 
-/* Arena capacities for sequences up to L_max; `scale` doubles on every regrowth. */
+/* Arena capacities for sequences up to L_max, about twice the high-water marks measured on
+ * the benchmark mix; `scale` grows on every regrowth after an overflow. */
 inline Caps make_caps(int L_max, const FoldParams &F, int nthreads, int scale) {
   Caps c;
   memset(&c, 0, sizeof c);
   int64_t mb = F.max_branch > 0 ? F.max_branch : 0;
   int64_t ms = F.max_stack;
+  int64_t mbc = mb < 4096LL * scale ? mb : 4096LL * scale; /* children kept per step */
   c.L_max = L_max < 16 ? 16 : L_max;
-  c.node_cap = (int32_t)((1024 + 32 * ms + 4 * (int64_t)L_max) * scale);
-  c.pool16_cap = c.node_cap * 32;
-  c.cand_cap = c.node_cap * 24;
-  c.store_cap = (int32_t)(1 + ms * 16 * scale);
-  c.nlist_cap = c.store_cap * 24;
-  c.new_cap = (int32_t)(mb + ms + nthreads + 1);
-  c.seen_cap = pow2_at_least(4 * (mb + ms + nthreads) * 16 * scale);
+  c.nwarps = nthreads >= 32 ? nthreads / 32 : 1;
+  c.chunk_cap = (int32_t)(4 * nthreads > ms ? 4 * nthreads : ms);
+  int64_t kmin = 2 * (int64_t)c.L_max > F.nb_mode ? 2 * (int64_t)c.L_max : F.nb_mode;
+  c.key_cap = pow2_at_least(kmin < 32 ? 32 : kmin);
+  c.mask_words = c.L_max / 32 + 2;
+  c.node_cap = (int32_t)((256 + 6 * ms + 2 * (int64_t)c.L_max) * scale);
+  c.pool16_cap = c.node_cap * 12;
+  int per_node = F.nb_mode / 4 < 8 ? 8 : F.nb_mode / 4 > 64 ? 64 : F.nb_mode / 4;
+  c.cand_cap = c.node_cap * per_node;
+  c.store_cap = (int32_t)(1 + ms * 12 * scale);
+  c.nlist_cap = c.store_cap * 12;
+  c.new_cap = (int32_t)(mbc + ms + 1);
+  c.seen_cap = pow2_at_least(16 * (mbc + ms) * scale + 64);
   c.nht_cap = pow2_at_least(4 * (int64_t)c.node_cap);
   c.step_cap = 48 * scale;
   c.todo_cap = (int32_t)(256 + 8 * ms) * scale;
+  WarpScratch W;
+  c.wscratch_bytes = (int32_t)wscratch_carve(W, nullptr, c, F);
   Arena A;
-  c.arena_bytes = (int64_t)arena_carve(A, nullptr, c, F, nthreads);
+  c.arena_bytes = (int64_t)arena_carve(A, nullptr, c, F);
   return c;
 }
 

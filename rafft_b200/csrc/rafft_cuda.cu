@@ -23,6 +23,9 @@
 using namespace rafft;
 
 #define RF_BLOCK_THREADS_MAX 256
+#ifndef RF_MIN_BLOCKS
+#define RF_MIN_BLOCKS 4 /* 64 registers per thread: 32 resident warps per SM */
+#endif
 
 /* ------------------------------------------------------------------------------------ */
 /* kernels                                                                               */
@@ -44,7 +47,7 @@ __global__ void order_kernel(const int64_t *__restrict__ offs, const int32_t *__
   order[r] = si;
 }
 
-__global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX)
+__global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX, RF_MIN_BLOCKS)
 fold_kernel(const DevEnergy *__restrict__ E, FoldParams prm, Caps caps, char *arenas,
             const char *__restrict__ seqs, const int64_t *__restrict__ offs,
             const int32_t *__restrict__ order, int n, OutBuf out) {
@@ -53,7 +56,7 @@ fold_kernel(const DevEnergy *__restrict__ E, FoldParams prm, Caps caps, char *ar
   __shared__ int next;
   if (threadIdx.x == 0) {
     f.E = E; f.prm = prm; f.caps = caps; f.sh = &sh;
-    arena_carve(f.A, arenas + (size_t)blockIdx.x * (size_t)caps.arena_bytes, caps, prm, blockDim.x);
+    arena_carve(f.A, arenas + (size_t)blockIdx.x * (size_t)caps.arena_bytes, caps, prm);
   }
   for (;;) {
     __syncthreads();
@@ -227,8 +230,11 @@ struct rafft_ctx {
   DevBuf arenas, seqs, offs, order, subset, idx, big, ordered, scan, evalbuf;
   std::vector<HostBlock> pinned_free;
   int64_t *h_small = nullptr; /* pinned: totals + cursors */
-  int block_threads = 128;
-  int blocks_per_sm = 8;
+  int block_threads = 64;
+  int blocks_per_sm = 16;
+  uint64_t arena_sig = 0;   /* layout of the arenas whose hash tables are known to be empty */
+  bool arena_dirty = true;
+  size_t arena_clean = 0;   /* leading bytes of the arena buffer known to be clean */
   std::string err;
 };
 
@@ -485,7 +491,25 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     int64_t grid = std::min<int64_t>(m, (int64_t)ctx->sm_count * ctx->blocks_per_sm);
     int64_t budget = (int64_t)((free_b + ctx->arenas.cap) * 0.6);
     if (grid * caps.arena_bytes > budget) grid = std::max<int64_t>(1, budget / caps.arena_bytes);
-    if (int rc = dev_reserve(ctx, ctx->arenas, (size_t)(grid * caps.arena_bytes))) return fail(rc);
+    {
+      /* The hash tables at the head of every arena must be empty before a run; a run leaves
+       * them empty again, so they are zeroed only when the buffer or its layout changes. */
+      void *before = ctx->arenas.p;
+      if (int rc = dev_reserve(ctx, ctx->arenas, (size_t)(grid * caps.arena_bytes))) return fail(rc);
+      uint64_t sig = 1469598103934665603ULL;
+      const unsigned char *cb = (const unsigned char *)&caps;
+      for (size_t k = 0; k < sizeof caps; k++) sig = (sig ^ cb[k]) * 1099511628211ULL;
+      const size_t need = (size_t)(grid * caps.arena_bytes);
+      if (before != ctx->arenas.p || sig != ctx->arena_sig || ctx->arena_dirty) {
+        CK(cudaMemsetAsync(ctx->arenas.p, 0, need, ctx->stream));
+        ctx->arena_sig = sig;
+        ctx->arena_dirty = false;
+        ctx->arena_clean = need;
+      } else if (need > ctx->arena_clean) {
+        CK(cudaMemsetAsync((char *)ctx->arenas.p + ctx->arena_clean, 0, need - ctx->arena_clean, ctx->stream));
+        ctx->arena_clean = need;
+      }
+    }
     /* queue */
     const int32_t *d_subset = nullptr;
     if (round > 0) {

@@ -34,10 +34,10 @@ int emu_fold(const rafft_energy_params *ep_in, const char *seq, int L, const raf
   Exec::order() = reverse;
   Exec::emu_threads() = nthreads > 0 ? nthreads : 32;
   Caps caps = make_caps(L, F, Exec::nthreads(), scale > 0 ? scale : 1);
-  std::vector<char> arena((size_t)caps.arena_bytes);
+  std::vector<char> arena((size_t)caps.arena_bytes, 0);  /* hash tables start empty */
   Fold f;
   f.E = D; f.prm = F; f.caps = caps;
-  arena_carve(f.A, arena.data(), caps, F, Exec::nthreads());
+  arena_carve(f.A, arena.data(), caps, F);
   BlockShared sh;
   f.sh = &sh;
   /* output for one sequence */
@@ -53,6 +53,12 @@ int emu_fold(const rafft_energy_params *ep_in, const char *seq, int L, const raf
   out.db = db.data(); out.step_n = step_n.data(); out.entries = entries.data(); out.cursors = cursors;
   out.struct_cap = scap; out.db_cap = (int64_t)db.size(); out.step_cap = caps.step_cap; out.entry_cap = ecap;
   f.run(seq, L, 0, out);
+  /* run() must leave the hash tables empty for the next sequence of the arena */
+  {
+    size_t tb = arena_table_bytes(caps);
+    for (size_t k = 0; k < tb; k++)
+      if (arena[k]) { fprintf(stderr, "emu_fold: hash tables not clean after run\n"); return -2; }
+  }
   if (cnt) for (int k = 0; k < CNT_N; k++) cnt[k] = counters[k];
   if (hiwater) {
     hiwater[0] = sh.n_node; hiwater[1] = sh.n_pool16; hiwater[2] = sh.n_cand; hiwater[3] = sh.n_store;
