@@ -71,10 +71,9 @@ struct Caps {
   int32_t step_cap;          /* folding steps */
   int32_t todo_cap;
   int32_t chunk_cap;         /* stem combinations examined per block phase */
-  int32_t nwarps;            /* warps per block = concurrent node expansions */
   int32_t key_cap;           /* per-warp sort keys: pow2 >= max(2*L_max, nb_mode) */
   int32_t mask_words;        /* 32-bit words per one-hot mask (L_max/32 + 2) */
-  int32_t wscratch_bytes;    /* per-warp expansion scratch */
+  int32_t wscratch_bytes;    /* scratch slot of one region expansion (TaskQueue::scratch) */
   int64_t arena_bytes;
 };
 
@@ -446,7 +445,6 @@ struct Arena {
   int32_t *flag, *pref; /* sel_cap = max(chunk_cap, new_cap + max_stack) */
   int32_t *ch_e;       /* chunk_cap */
   uint64_t *ch_lo, *ch_hi; /* chunk_cap */
-  char *wscratch;      /* nwarps * wscratch_bytes: node expansion scratch, one per warp */
 };
 
 /* Scratch of one node expansion (views into the warp's slice of Arena::wscratch). */
@@ -462,14 +460,30 @@ struct WarpScratch {
   int32_t *tmp;     /* 8 ints */
 };
 
-struct BlockShared {
+/* Per-sequence state that lives across the phase kernels (global memory; the block-scope
+ * kernels work on a shared-memory copy). */
+struct SeqState {
   int32_t seq_index, L, status;
+  int32_t active;          /* 0 once the fold has converged or failed */
+  int32_t stage;           /* 0: a new folding step starts (record the beam), 1: expansion under way */
+  int32_t expand_pending;  /* some region of the beam could not be queued this round */
   int32_t n_node, n_pool16, n_cand, n_store, n_nlist, n_seen, n_todo, n_expand;
   int32_t beam_n, n_new, nb_branch, n_steps, n_traj;
   int32_t tmp0, tmp1, tmp2, cur_b, xcut;
   int32_t emin, emax, cnt_le;
   int32_t wsum[12];
+  int64_t seq_off;         /* first letter of the sequence in the batch text */
   unsigned long long cnt[CNT_N];
+};
+typedef SeqState BlockShared;
+
+/* Region-expansion work list of one round: (sequence slot, node id) + one scratch slot each. */
+struct TaskQueue {
+  int32_t *n_tasks;   /* device counter; may overshoot cap */
+  int32_t cap;
+  int32_t *task;      /* 2 ints per task */
+  char *scratch;      /* cap * caps.wscratch_bytes */
+  int32_t self;       /* slot of the sequence this Fold works on (block scope) */
 };
 
 RF_HD size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
@@ -531,11 +545,72 @@ RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &
   RF_CARVE(ch_e, int32_t, c.chunk_cap);
   RF_CARVE(ch_lo, uint64_t, c.chunk_cap);
   RF_CARVE(ch_hi, uint64_t, c.chunk_cap);
-  off = align_up(off, 128);
-  RF_CARVE(wscratch, char, (size_t)c.nwarps * c.wscratch_bytes);
 #undef RF_CARVE
   return align_up(off, 256);
 }
+/* Byte offsets of the arena pieces (computed once on the host, bound per block/warp). */
+struct ArenaOff {
+  uint32_t seen, nht, code, node, pool16, cand, store, store_db, nlist, ncnt, seen_used, fresh, sel, sel_idx, sel_store, beam, traj_n, traj, todo, todo_id, flag, pref, ch_e, ch_lo, ch_hi;
+};
+RF_HD void arena_bind(Arena &A, char *base, const ArenaOff &o) {
+  A.seen = (SeenEnt *)(base + o.seen);
+  A.nht = (unsigned long long *)(base + o.nht);
+  A.code = (uint8_t *)(base + o.code);
+  A.node = (NodeRec *)(base + o.node);
+  A.pool16 = (int16_t *)(base + o.pool16);
+  A.cand = (Cand *)(base + o.cand);
+  A.store = (StoreRec *)(base + o.store);
+  A.store_db = (char *)(base + o.store_db);
+  A.nlist = (int32_t *)(base + o.nlist);
+  A.ncnt = (int32_t *)(base + o.ncnt);
+  A.seen_used = (int32_t *)(base + o.seen_used);
+  A.fresh = (NewRec *)(base + o.fresh);
+  A.sel = (int32_t *)(base + o.sel);
+  A.sel_idx = (int32_t *)(base + o.sel_idx);
+  A.sel_store = (int32_t *)(base + o.sel_store);
+  A.beam = (int32_t *)(base + o.beam);
+  A.traj_n = (int32_t *)(base + o.traj_n);
+  A.traj = (int32_t *)(base + o.traj);
+  A.todo = (int32_t *)(base + o.todo);
+  A.todo_id = (int32_t *)(base + o.todo_id);
+  A.flag = (int32_t *)(base + o.flag);
+  A.pref = (int32_t *)(base + o.pref);
+  A.ch_e = (int32_t *)(base + o.ch_e);
+  A.ch_lo = (uint64_t *)(base + o.ch_lo);
+  A.ch_hi = (uint64_t *)(base + o.ch_hi);
+}
+#ifndef __CUDACC_RTC__
+inline void arena_offsets(ArenaOff &o, const Caps &c, const FoldParams &fp) {
+  Arena A;
+  char *base = (char *)4096;
+  arena_carve(A, base, c, fp);
+  o.seen = (uint32_t)((char *)A.seen - base);
+  o.nht = (uint32_t)((char *)A.nht - base);
+  o.code = (uint32_t)((char *)A.code - base);
+  o.node = (uint32_t)((char *)A.node - base);
+  o.pool16 = (uint32_t)((char *)A.pool16 - base);
+  o.cand = (uint32_t)((char *)A.cand - base);
+  o.store = (uint32_t)((char *)A.store - base);
+  o.store_db = (uint32_t)((char *)A.store_db - base);
+  o.nlist = (uint32_t)((char *)A.nlist - base);
+  o.ncnt = (uint32_t)((char *)A.ncnt - base);
+  o.seen_used = (uint32_t)((char *)A.seen_used - base);
+  o.fresh = (uint32_t)((char *)A.fresh - base);
+  o.sel = (uint32_t)((char *)A.sel - base);
+  o.sel_idx = (uint32_t)((char *)A.sel_idx - base);
+  o.sel_store = (uint32_t)((char *)A.sel_store - base);
+  o.beam = (uint32_t)((char *)A.beam - base);
+  o.traj_n = (uint32_t)((char *)A.traj_n - base);
+  o.traj = (uint32_t)((char *)A.traj - base);
+  o.todo = (uint32_t)((char *)A.todo - base);
+  o.todo_id = (uint32_t)((char *)A.todo_id - base);
+  o.flag = (uint32_t)((char *)A.flag - base);
+  o.pref = (uint32_t)((char *)A.pref - base);
+  o.ch_e = (uint32_t)((char *)A.ch_e - base);
+  o.ch_lo = (uint32_t)((char *)A.ch_lo - base);
+  o.ch_hi = (uint32_t)((char *)A.ch_hi - base);
+}
+#endif
 /* bytes at the start of an arena that hold the hash tables (zeroed by the host once) */
 RF_HD size_t arena_table_bytes(const Caps &c) {
   return align_up(sizeof(SeenEnt) * (size_t)c.seen_cap, 16) + sizeof(unsigned long long) * (size_t)c.nht_cap;
@@ -544,11 +619,13 @@ RF_HD size_t arena_table_bytes(const Caps &c) {
 /* ------------------------------------------------------------------------------------ */
 struct Fold {
   const DevEnergy *E;
-  FoldParams prm;
-  Caps caps;
+  const FoldParams &prm;
+  const Caps &caps;
   Arena A;
-  BlockShared *sh;
+  SeqState *sh;
   EnergyView ev;
+  TaskQueue Q;
+  RF_HD Fold(const DevEnergy *E_, const FoldParams &p, const Caps &c) : E(E_), prm(p), caps(c) {}
 
   /* --- node geometry ------------------------------------------------------------------ */
   RF_FN const int16_t *node_br(const NodeRec &n) const { return A.pool16 + n.pool_off; }
@@ -604,7 +681,7 @@ struct Fold {
   /* --- node creation --------------------------------------------------------------------
    * Fill node record `id` for the loop closed by (ci,cj) with branches copied from parent
    * ranges.  Returns false on pool overflow. */
-  RF_NOINLINE bool build_node(int id, int ci, int cj, const NodeRec *par, int lo1, int hi1, int xp, int xq,
+  RF_FN bool build_node(int id, int ci, int cj, const NodeRec *par, int lo1, int hi1, int xp, int xq,
                         int lo2, int hi2, int lv) {
     int m = (hi1 - lo1) + (xp >= 0 ? 1 : 0) + (hi2 - lo2);
     int need = 2 * m + m + 2;
@@ -645,7 +722,7 @@ struct Fold {
     return true;
   }
   /* Insert node `id` into the unique-loop table or find the identical loop already there. */
-  RF_NOINLINE int nht_resolve(int id) {
+  RF_FN int nht_resolve(int id) {
     NodeRec &n = A.node[id];
     unsigned long long tag = ((n.hash >> 32) << 32) | (unsigned)(id + 1);
     unsigned mask = caps.nht_cap - 1;
@@ -666,7 +743,7 @@ struct Fold {
   }
 
   /* --- warp-scope bitonic sort of n (power of two) 64-bit keys ---------------------------- */
-  RF_NOINLINE void wsort(uint64_t *keys, int n, bool descending) {
+  RF_NOINLINE static void wsort(uint64_t *keys, int n, bool descending) {
     for (int k = 2; k <= n; k <<= 1) {
       for (int j = k >> 1; j > 0; j >>= 1) {
         RF_WPAR_BEGIN(t, n >> 1)
@@ -697,16 +774,21 @@ struct Fold {
     return Exec::funnel_r(mword(M, a, nw), mword(M, a + 1, nw), b);
   }
 
-  RF_NOINLINE void expand_node(int v, int wslot) {
-    NodeRec &n = A.node[v];
-    const int lv = n.lv, m = n.br_n;
-    const int nlag = 2 * lv - 1;
-    const int nw = (lv + 31) >> 5, MW = caps.mask_words;
-    WarpScratch W;
-    wscratch_carve(W, A.wscratch + (size_t)wslot * (size_t)caps.wscratch_bytes, caps, prm);
-    uint32_t *const F = W.mask, *const R = W.mask + 4 * MW, *const CL = W.mask + 8 * MW,
-                   *const CLR = W.mask + 9 * MW;
-    const uint8_t *const code = A.code;
+#define RF_EXPAND_VARS                                                                         \
+  const int lv = n.lv, m = n.br_n;                                                             \
+  const int nlag = 2 * lv - 1;                                                                 \
+  const int nw = (lv + 31) >> 5, MW = caps.mask_words;                                         \
+  uint32_t *const F = W.mask, *const R = W.mask + 4 * MW, *const CL = W.mask + 8 * MW,         \
+                 *const CLR = W.mask + 9 * MW;                                                 \
+  const uint8_t *const code = A.code;                                                          \
+  int nk = 32;                                                                                 \
+  while (nk < nlag) nk <<= 1;                                                                  \
+  const int nr = nlag < prm.nb_mode ? nlag : prm.nb_mode;                                      \
+  (void)m; (void)nw; (void)F; (void)R; (void)CL; (void)CLR; (void)code; (void)nk; (void)nr;
+
+  /* Warp-scope phases of one region expansion; W is the task's scratch slot. */
+  RF_FN void expand_e1(NodeRec &n, WarpScratch &W) {
+    RF_EXPAND_VARS
     /* 1. local index -> original position / branch count; one-hot masks; contiguity masks
      *    (CL bit t: position t continues position t-1 in ORIGINAL coordinates) */
     RF_WPAR_BEGIN(x, 10 * MW)
@@ -734,8 +816,6 @@ struct Fold {
      *    c[p] = cor[p] / (min(p, 2lv-2-p) + 1.0) as the reference's float64.
      *    key = order-preserving bits of c[p] with the lag in the low bits, so that sorting
      *    keys descending is the reference's (value desc, lag desc) order (rafft.py:118,92). */
-    int nk = 32;
-    while (nk < nlag) nk <<= 1;
     const int wGC = prm.wi[1][2], wAU = prm.wi[0][3], wGU = prm.wi[2][3];
     RF_WPAR_BEGIN(p, nk)
       uint64_t key = 0;
@@ -755,12 +835,17 @@ struct Fold {
       }
       W.keys[p] = key;
     RF_WPAR_END
+  }
+  RF_FN void expand_e2(NodeRec &n, WarpScratch &W) {
+    RF_EXPAND_VARS
     /* 3. rank: the first nb_mode lags in (value desc, lag desc) order */
     wsort(W.keys, nk, true);
-    const int nr = nlag < prm.nb_mode ? nlag : prm.nb_mode;
     RF_WPAR_BEGIN(r, nr)
       W.ranked[r] = (int)(W.keys[r] & 0x1FFFULL);
     RF_WPAR_END
+  }
+  RF_FN void expand_e3(NodeRec &n, WarpScratch &W) {
+    RF_EXPAND_VARS
     /* 4. per ranked lag: best-scoring consecutive stem (window_slide, rafft.py:36-83), walking
      *    only the positions whose pair weight is non-zero, and the energy change of forming
      *    it (eval_one_struct difference, rafft.py:98). */
@@ -805,6 +890,17 @@ struct Fold {
           last_i = i;
         }
       }
+      W.r_stem[r] = ((uint32_t)max_i << 16) | (uint32_t)max_j;
+      W.r_nb[r] = max_nb;
+      Exec::atomic_add(&W.tmp[0], len2);
+    RF_WPAR_END
+  }
+  RF_FN void expand_e4(NodeRec &n, WarpScratch &W) {
+    RF_EXPAND_VARS
+    /* the energy change of forming each stem (eval_one_struct difference, rafft.py:98) */
+    RF_WPAR_BEGIN(r, nr)
+      const int max_nb = W.r_nb[r];
+      const int max_i = (int)(W.r_stem[r] >> 16), max_j = (int)(W.r_stem[r] & 0xffff);
       int dE = 0x7fffffff;
       if (max_nb > 0) {
         const int16_t *br = node_br(n);
@@ -829,15 +925,15 @@ struct Fold {
         dE = e - n.e_loop;
       }
       W.r_dE[r] = dE;
-      W.r_stem[r] = ((uint32_t)max_i << 16) | (uint32_t)max_j;
-      W.r_nb[r] = max_nb;
       /* 5. stems below the threshold get a (dE, rank) key: stable order by dE (rafft.py:108) */
       const bool kept = max_nb > 0 && dE < prm.cand_thr;
       W.keys[r] = kept ? (((uint64_t)(uint32_t)(dE ^ 0x80000000)) << 32) | (uint32_t)r : ~0ULL;
-      Exec::atomic_add(&W.tmp[0], len2);
       if (max_nb > 0) Exec::atomic_add(&W.tmp[1], 1);
       if (kept) Exec::atomic_add(&W.tmp[2], 1);
     RF_WPAR_END
+  }
+  RF_FN void expand_e5(NodeRec &n, WarpScratch &W) {
+    RF_EXPAND_VARS
     int nrp = 32;
     while (nrp < nr) nrp <<= 1;
     RF_WPAR_BEGIN(r, nrp - nr)
@@ -878,6 +974,13 @@ struct Fold {
       n.cand_off = off < 0 ? 0 : off;
       n.cand_n = off < 0 ? 0 : keep_n;
     RF_WSINGLE_END
+  }
+  /* all phases in a row (host emulation) */
+  RF_FN void expand_node(int v, char *slot) {
+    WarpScratch W;
+    wscratch_carve(W, slot, caps, prm);
+    NodeRec &n = A.node[v];
+    expand_e1(n, W); expand_e2(n, W); expand_e3(n, W); expand_e4(n, W); expand_e5(n, W);
   }
 
   /* --- seen set (global per sequence, rafft.py:196-200) ------------------------------- */
@@ -921,13 +1024,15 @@ struct Fold {
   }
 
   /* ------------------------------------------------------------------------------------ */
-  RF_NOINLINE void run(const char *seq, int L, int seq_index, OutBuf &out) {
+  /* ---- phase: start of a fold ---------------------------------------------------------- */
+  RF_FN void phase_init(const char *seq, int L, int seq_index) {
     /* ---- reset per-sequence state */
     RF_SINGLE_BEGIN
       sh->seq_index = seq_index; sh->L = L; sh->status = ST_OK;
       sh->n_node = 0; sh->n_pool16 = 0; sh->n_cand = 0; sh->n_store = 0; sh->n_nlist = 0;
       sh->n_seen = 0; sh->n_todo = 0; sh->n_expand = 0; sh->beam_n = 0; sh->n_new = 0;
       sh->nb_branch = 0; sh->n_steps = 0; sh->n_traj = 0;
+      sh->active = 1; sh->stage = 0; sh->expand_pending = 0;
       for (int k = 0; k < CNT_N; k++) sh->cnt[k] = 0;
       sh->cnt[CNT_T0_NS] = (unsigned long long)Exec::now_ns();
       if (L > caps.L_max) sh->status = ST_ERR_CAPACITY;
@@ -955,10 +1060,14 @@ struct Fold {
         sh->n_nlist = 1; sh->n_store = 1;
         A.beam[0] = 0; sh->beam_n = 1;
       RF_SINGLE_END
-      while (sh->status == ST_OK) {
-        if (!step()) break;
-      }
     }
+    RF_SINGLE_BEGIN
+      if (sh->status != ST_OK) sh->active = 0;
+    RF_SINGLE_END
+  }
+
+  /* ---- phase: results out, hash tables left empty for the next sequence of this arena ---- */
+  RF_FN void phase_finish(OutBuf &out) {
     emit(out);
     /* leave the two hash tables empty for the next sequence of this arena */
     RF_PAR_BEGIN(i, sh->n_seen)
@@ -971,44 +1080,56 @@ struct Fold {
     RF_PAR_END
   }
 
-  /* One bfs_pairs call (rafft.py:156-216).  Returns false when the beam has converged. */
-  RF_NOINLINE bool step() {
-    const int L = sh->L;
+  RF_FN void bind_ev() { ev.P = E; ev.s = A.code; ev.L = sh->L; }
+  RF_FN void finish_fold() { /* block scope: the fold has converged or failed */
+    RF_SINGLE_BEGIN
+      sh->active = 0;
+      sh->cnt[CNT_T1_NS] = (unsigned long long)Exec::now_ns();
+    RF_SINGLE_END
+  }
+
+  /* One bfs_pairs call (rafft.py:156-216) is a sequence of phases:
+   *   gather -> [region expansions e1..e5, warp tasks] -> combine -> select -> materialise.
+   * ---- phase: record the beam (once per step) and queue the regions still to be expanded */
+  RF_FN void phase_gather() {
+    if (!sh->active) return;
     const int beam_n = sh->beam_n;
     /* glob_traj += [glob_tree] (rafft.py:161) */
     RF_SINGLE_BEGIN
-      if (sh->n_steps >= caps.step_cap) fail(ST_ERR_CAPACITY);
-      else {
-        A.traj_n[sh->n_steps] = beam_n;
-        for (int b = 0; b < beam_n; b++) A.traj[(size_t)sh->n_steps * prm.max_stack + b] = A.beam[b];
-        sh->n_steps++;
-        sh->cnt[CNT_STEPS]++;
+      if (sh->stage == 0) {
+        if (sh->n_steps >= caps.step_cap) fail(ST_ERR_CAPACITY);
+        else {
+          A.traj_n[sh->n_steps] = beam_n;
+          for (int b = 0; b < beam_n; b++) A.traj[(size_t)sh->n_steps * prm.max_stack + b] = A.beam[b];
+          sh->n_steps++;
+          sh->cnt[CNT_STEPS]++;
+        }
+        sh->stage = 1;
       }
-      sh->n_expand = 0;
+      sh->expand_pending = 0;
     RF_SINGLE_END
-    if (sh->status != ST_OK) return false;
-
-    /* ---- P1: expand the loops of the beam that have not been expanded yet, one warp each */
+    if (sh->status != ST_OK) { finish_fold(); return; }
+    /* P1: the loops of the beam that have not been expanded yet become warp tasks */
     RF_PAR_BEGIN(b, beam_n)
       const StoreRec &S = A.store[A.beam[b]];
       if (!S.done) {
         for (int k = 0; k < S.nl_n; k++) {
           int v = A.nlist[S.nl_off + k];
           if (A.node[v].cand_n == -1 && Exec::atomic_cas(&A.node[v].cand_n, -1, -2) == -1) {
-            int at = Exec::atomic_add(&sh->n_expand, 1);
-            if (at < caps.todo_cap) A.todo_id[at] = v;
+            int at = Exec::atomic_add(Q.n_tasks, 1);
+            if (at < Q.cap) { Q.task[2 * at] = Q.self; Q.task[2 * at + 1] = v; }
+            else { A.node[v].cand_n = -1; sh->expand_pending = 1; } /* next round */
           }
         }
       }
     RF_PAR_END
-    if (sh->n_expand > caps.todo_cap) { RF_SINGLE_BEGIN fail(ST_ERR_CAPACITY); RF_SINGLE_END return false; }
-    {
-      const int ne = sh->n_expand;
-      for (int a = Exec::warp(); a < ne; a += Exec::nwarps()) expand_node(A.todo_id[a], Exec::warp());
-      Exec::sync();
-    }
-    if (sh->status != ST_OK) return false;
+  }
 
+  /* ---- phase: combine stems of independent regions (rafft.py:176-203) */
+  RF_FN void phase_combine() {
+    if (!sh->active || sh->expand_pending) return;
+    if (sh->status != ST_OK) { finish_fold(); return; }
+    const int beam_n = sh->beam_n;
     /* ---- P2: combine stems of independent regions (rafft.py:176-203) */
     /* P2a: per beam member, how many stems of each of its regions pass (rafft.py:102), the size
      *      of its product, and the reference's work counters (create_childs runs for every
@@ -1109,7 +1230,7 @@ struct Fold {
         sh->cur_b = b + 1;
       RF_SINGLE_END
     }
-    if (sh->status != ST_OK) return false;
+    if (sh->status != ST_OK) { finish_fold(); return; }
     /* P2c: once nb_branch >= max_branch the `break` only leaves the product loop
      *      (rafft.py:202-203): every later member still tries its first combination */
     {
@@ -1150,8 +1271,13 @@ struct Fold {
         RF_SINGLE_END
       }
     }
-    if (sh->status != ST_OK) return false;
+    if (sh->status != ST_OK) finish_fold();
+  }
 
+  /* ---- phase: the next beam */
+  RF_FN void phase_select() {
+    if (!sh->active || sh->expand_pending) return;
+    const int beam_n = sh->beam_n;
     /* ---- P3: new + old, stable sort by energy, keep max_stack (rafft.py:206-210).
      *      Entry i < n_new is a new child (generation order), then the old beam in order;
      *      the order is (energy, i).  Selection: bisect the energy threshold T of the
@@ -1239,9 +1365,17 @@ struct Fold {
       if (sh->n_store + nfresh > caps.store_cap) fail(ST_ERR_CAPACITY);
       sh->n_todo = 0;
     RF_SINGLE_END
-    if (sh->status != ST_OK || sh->tmp0) return false;
+    if (sh->status != ST_OK || sh->tmp0) finish_fold();
+  }
 
-    /* ---- P4: materialise the selected new children (dot-bracket, node list) */
+  /* ---- phase: materialise the selected new children (dot-bracket, node list) */
+  RF_FN void phase_materialise() {
+    if (!sh->active || sh->expand_pending) return;
+    const int L = sh->L;
+    const int beam_n = sh->beam_n;
+    const int n_new = sh->n_new;
+    const int total = n_new + beam_n;
+    const int keep = total < prm.max_stack ? total : prm.max_stack;
     /* 4a. which child regions (inner / outer of the chosen stems) are not known yet */
     RF_PAR_BEGIN(r, keep)
       int i = A.sel[r];
@@ -1274,7 +1408,7 @@ struct Fold {
         A.sel_store[r] = cnt_nodes; /* node count of the child, reused in 4d */
       }
     RF_PAR_END
-    if (sh->n_todo > caps.todo_cap) { RF_SINGLE_BEGIN fail(ST_ERR_CAPACITY); RF_SINGLE_END return false; }
+    if (sh->n_todo > caps.todo_cap) { RF_SINGLE_BEGIN fail(ST_ERR_CAPACITY); RF_SINGLE_END finish_fold(); return; }
     const int n_todo = sh->n_todo;
     /* 4b. build the loop records */
     RF_SINGLE_BEGIN
@@ -1282,25 +1416,25 @@ struct Fold {
       if (sh->n_node + n_todo > caps.node_cap) fail(ST_ERR_CAPACITY);
       else sh->n_node += n_todo;
     RF_SINGLE_END
-    if (sh->status != ST_OK) return false;
+    if (sh->status != ST_OK) { finish_fold(); return; }
     const int node_base = sh->tmp2;
     RF_PAR_BEGIN(a, n_todo)
       const NodeRec &par = A.node[A.todo[3 * a]];
       const Cand &cd = A.cand[par.cand_off + A.todo[3 * a + 1]];
       int side = A.todo[3 * a + 2];
       int mip = cd.mip, mjp = cd.mjp, nb = cd.nb;
-      bool ok;
+      int ci, cj, lo1, hi1, xp, xq, lo2, hi2, clv;
       if (side == 0) { /* get_inner_loop (utils.py:148-152): local (mip, mjp) exclusive */
-        ok = build_node(node_base + a, pos_of(par, mip), pos_of(par, mjp), &par, seg_of(par, mip),
-                        seg_of(par, mjp), -1, -1, 0, 0, mjp - mip - 1);
+        ci = pos_of(par, mip); cj = pos_of(par, mjp); lo1 = seg_of(par, mip); hi1 = seg_of(par, mjp);
+        xp = -1; xq = -1; lo2 = 0; hi2 = 0; clv = mjp - mip - 1;
       } else { /* get_outer_loop (utils.py:141-145): local [0, mip-nb] ++ [mjp+nb, lv) */
         int io = mip - nb + 1, jo = mjp + nb - 1;
-        ok = build_node(node_base + a, par.ci, par.cj, &par, 0, seg_of(par, io), pos_of(par, io),
-                        pos_of(par, jo), seg_of(par, jo), par.br_n, io + (par.lv - 1 - jo));
+        ci = par.ci; cj = par.cj; lo1 = 0; hi1 = seg_of(par, io); xp = pos_of(par, io); xq = pos_of(par, jo);
+        lo2 = seg_of(par, jo); hi2 = par.br_n; clv = io + (par.lv - 1 - jo);
       }
-      if (!ok) fail(ST_ERR_CAPACITY);
+      if (!build_node(node_base + a, ci, cj, &par, lo1, hi1, xp, xq, lo2, hi2, clv)) fail(ST_ERR_CAPACITY);
     RF_PAR_END
-    if (sh->status != ST_OK) return false;
+    if (sh->status != ST_OK) { finish_fold(); return; }
     /* 4c. unify identical loops reached through different stems / orders */
     RF_PAR_BEGIN(a, n_todo)
       int id = nht_resolve(node_base + a);
@@ -1308,7 +1442,7 @@ struct Fold {
       Cand &cd = A.cand[A.node[A.todo[3 * a]].cand_off + A.todo[3 * a + 1]];
       if (A.todo[3 * a + 2]) cd.outer_id = id; else cd.inner_id = id;
     RF_PAR_END
-    if (sh->status != ST_OK) return false;
+    if (sh->status != ST_OK) { finish_fold(); return; }
     /* 4d. store records + node lists (in_side then out_side per stem, rafft.py:187-190) */
     RF_SINGLE_BEGIN
       int at = sh->n_store, nl = sh->n_nlist;
@@ -1327,7 +1461,7 @@ struct Fold {
       if (nl > caps.nlist_cap) fail(ST_ERR_CAPACITY);
       else { sh->n_nlist = nl; sh->n_store = at; }
     RF_SINGLE_END
-    if (sh->status != ST_OK) return false;
+    if (sh->status != ST_OK) { finish_fold(); return; }
     /* copy the parent's dot-bracket */
     RF_PAR_BEGIN(x, keep * L)
       int r = x / L, pos = x - r * L;
@@ -1371,12 +1505,12 @@ struct Fold {
       }
       for (int r = 0; r < keep; r++) A.beam[r] = A.sel[r];
       sh->beam_n = keep;
+      sh->stage = 0;
     RF_SINGLE_END
-    return true;
   }
 
   /* Copy the result of this sequence into the global output (bump allocation). */
-  RF_NOINLINE void emit(OutBuf &out) {
+  RF_FN void emit(OutBuf &out) {
     const int L = sh->L, si = sh->seq_index;
     RF_SINGLE_BEGIN
       int nstruct = 0, nstep = 0, nentry = 0;
@@ -1402,7 +1536,6 @@ struct Fold {
       out.seq_db[si] = (int64_t)d0;
       out.seq_step[si] = (int64_t)t0; out.seq_nstep[si] = nstep;
       out.seq_entry[si] = (int64_t)e0;
-      sh->cnt[CNT_T1_NS] = (unsigned long long)Exec::now_ns();
       for (int k = 0; k < CNT_N; k++) out.counters[(size_t)si * CNT_N + k] = (int64_t)sh->cnt[k];
       sh->tmp0 = nstruct;
     RF_SINGLE_END

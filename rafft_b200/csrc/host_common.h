@@ -142,7 +142,6 @@ inline Caps make_caps(int L_max, const FoldParams &F, int nthreads, int scale) {
   int64_t ms = F.max_stack;
   int64_t mbc = mb < 4096LL * scale ? mb : 4096LL * scale; /* children kept per step */
   c.L_max = L_max < 16 ? 16 : L_max;
-  c.nwarps = nthreads >= 32 ? nthreads / 32 : 1;
   c.chunk_cap = (int32_t)(4 * nthreads > ms ? 4 * nthreads : ms);
   int64_t kmin = 2 * (int64_t)c.L_max > F.nb_mode ? 2 * (int64_t)c.L_max : F.nb_mode;
   c.key_cap = pow2_at_least(kmin < 32 ? 32 : kmin);

@@ -23,9 +23,6 @@
 using namespace rafft;
 
 #define RF_BLOCK_THREADS_MAX 256
-#ifndef RF_MIN_BLOCKS
-#define RF_MIN_BLOCKS 4 /* 64 registers per thread: 32 resident warps per SM */
-#endif
 
 /* ------------------------------------------------------------------------------------ */
 /* kernels                                                                               */
@@ -47,26 +44,124 @@ __global__ void order_kernel(const int64_t *__restrict__ offs, const int32_t *__
   order[r] = si;
 }
 
-__global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX, RF_MIN_BLOCKS)
-fold_kernel(const DevEnergy *__restrict__ E, FoldParams prm, Caps caps, char *arenas,
-            const char *__restrict__ seqs, const int64_t *__restrict__ offs,
-            const int32_t *__restrict__ order, int n, OutBuf out) {
-  __shared__ Fold f;
-  __shared__ BlockShared sh;
-  __shared__ int next;
-  if (threadIdx.x == 0) {
-    f.E = E; f.prm = prm; f.caps = caps; f.sh = &sh;
-    arena_carve(f.A, arenas + (size_t)blockIdx.x * (size_t)caps.arena_bytes, caps, prm);
+/* Everything the phase kernels of one wave need (kernel parameter, constant bank).
+ * A wave = `n` sequences folded together; slot j of the wave works on sequence order[j], owns
+ * arena j and state j.  The fold of a sequence is a chain of small kernels per folding
+ * step: each kernel's hot code fits the instruction cache and every
+ * resident warp runs the same phase. */
+struct WaveCtx {
+  const DevEnergy *E;
+  FoldParams prm;
+  Caps caps;
+  ArenaOff aoff;
+  char *arenas;
+  SeqState *states;
+  const char *seqs;
+  const int64_t *offs;
+  const int32_t *order;
+  int32_t n;
+  TaskQueue Q;
+  int32_t *n_active;
+  OutBuf out;
+};
+
+#define RF_WAVE_PARAM const __grid_constant__ WaveCtx c
+
+/* block-scope kernels: one block per wave slot, state staged through shared memory */
+struct BlockBind {
+  __device__ __forceinline__ static bool load(const WaveCtx &c, Fold &f, SeqState *sh, bool need_active) {
+    const int j = blockIdx.x;
+    SeqState *st = c.states + j;
+    if (need_active && !st->active) return false;
+    for (int k = threadIdx.x; k < (int)(sizeof(SeqState) / 4); k += blockDim.x) ((int *)sh)[k] = ((const int *)st)[k];
+    arena_bind(f.A, c.arenas + (size_t)j * (size_t)c.caps.arena_bytes, c.aoff);
+    f.sh = sh;
+    f.Q = c.Q;
+    f.Q.self = j;
+    __syncthreads();
+    f.bind_ev();
+    return true;
   }
-  for (;;) {
+  __device__ __forceinline__ static void store(const WaveCtx &c, SeqState *sh) {
     __syncthreads();
-    if (threadIdx.x == 0) next = (int)atomicAdd(&out.cursors[4], 1ULL);
-    __syncthreads();
-    const int q = next;
-    if (q >= n) break;
-    const int si = order[q];
-    const int64_t o = offs[si];
-    f.run(seqs + o, (int)(offs[si + 1] - o), si, out);
+    SeqState *st = c.states + blockIdx.x;
+    for (int k = threadIdx.x; k < (int)(sizeof(SeqState) / 4); k += blockDim.x) ((int *)st)[k] = ((const int *)sh)[k];
+  }
+};
+
+__global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_init(RF_WAVE_PARAM) {
+  __shared__ SeqState sh;
+  Fold f(c.E, c.prm, c.caps);
+  const int j = blockIdx.x;
+  arena_bind(f.A, c.arenas + (size_t)j * (size_t)c.caps.arena_bytes, c.aoff);
+  f.sh = &sh;
+  const int si = c.order[j];
+  const int64_t o = c.offs[si];
+  if (threadIdx.x == 0) sh.seq_off = o;
+  f.phase_init(c.seqs + o, (int)(c.offs[si + 1] - o), si);
+  BlockBind::store(c, &sh);
+}
+
+__global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_gather(RF_WAVE_PARAM) {
+  __shared__ SeqState sh;
+  Fold f(c.E, c.prm, c.caps);
+  if (!BlockBind::load(c, f, &sh, true)) return;
+  f.phase_gather();
+  BlockBind::store(c, &sh);
+}
+
+__global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_combine(RF_WAVE_PARAM) {
+  __shared__ SeqState sh;
+  Fold f(c.E, c.prm, c.caps);
+  if (!BlockBind::load(c, f, &sh, true)) return;
+  f.phase_combine();
+  BlockBind::store(c, &sh);
+}
+
+__global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_select(RF_WAVE_PARAM) {
+  __shared__ SeqState sh;
+  Fold f(c.E, c.prm, c.caps);
+  if (!BlockBind::load(c, f, &sh, true)) return;
+  f.phase_select();
+  BlockBind::store(c, &sh);
+}
+
+__global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_materialise(RF_WAVE_PARAM) {
+  __shared__ SeqState sh;
+  Fold f(c.E, c.prm, c.caps);
+  if (!BlockBind::load(c, f, &sh, true)) return;
+  f.phase_materialise();
+  if (threadIdx.x == 0 && sh.active) atomicAdd(c.n_active, 1);
+  BlockBind::store(c, &sh);
+}
+
+__global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_finish(RF_WAVE_PARAM) {
+  __shared__ SeqState sh;
+  Fold f(c.E, c.prm, c.caps);
+  BlockBind::load(c, f, &sh, false);
+  OutBuf out = c.out;
+  f.phase_finish(out);
+}
+
+/* warp-scope kernels: one warp per queued region, grid-stride over the work list */
+template <int PHASE>
+__global__ void __launch_bounds__(128) k_expand(RF_WAVE_PARAM) {
+  const int nt = min(*c.Q.n_tasks, c.Q.cap);
+  const int wpb = blockDim.x >> 5;
+  for (int t = blockIdx.x * wpb + (threadIdx.x >> 5); t < nt; t += gridDim.x * wpb) {
+    const int j = c.Q.task[2 * t], v = c.Q.task[2 * t + 1];
+    Fold f(c.E, c.prm, c.caps);
+    arena_bind(f.A, c.arenas + (size_t)j * (size_t)c.caps.arena_bytes, c.aoff);
+    f.sh = c.states + j;
+    f.bind_ev();
+    WarpScratch W;
+    wscratch_carve(W, c.Q.scratch + (size_t)t * (size_t)c.caps.wscratch_bytes, c.caps, c.prm);
+    NodeRec &n = f.A.node[v];
+    if (PHASE == 1) f.expand_e1(n, W);
+    if (PHASE == 2) f.expand_e2(n, W);
+    if (PHASE == 3) f.expand_e3(n, W);
+    if (PHASE == 4) f.expand_e4(n, W);
+    if (PHASE == 5) f.expand_e5(n, W);
   }
 }
 
@@ -227,11 +322,13 @@ struct rafft_ctx {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   DevEnergy *d_energy = nullptr;
-  DevBuf arenas, seqs, offs, order, subset, idx, big, ordered, scan, evalbuf;
+  DevBuf arenas, seqs, offs, order, subset, idx, big, ordered, scan, evalbuf, states, tasks, scratch, small;
   std::vector<HostBlock> pinned_free;
   int64_t *h_small = nullptr; /* pinned: totals + cursors */
-  int block_threads = 64;
-  int blocks_per_sm = 16;
+  int block_threads = 64;   /* threads per block of the block-scope phase kernels */
+  int blocks_per_sm = 16;   /* grid of the warp-task kernels: blocks per SM */
+  int64_t max_wave = 0;     /* sequences folded together (0 = as many as memory allows) */
+  int64_t max_tasks = 0;    /* capacity of the region work list (0 = automatic) */
   uint64_t arena_sig = 0;   /* layout of the arenas whose hash tables are known to be empty */
   bool arena_dirty = true;
   size_t arena_clean = 0;   /* leading bytes of the arena buffer known to be clean */
@@ -307,6 +404,7 @@ void rafft_destroy(rafft_ctx *ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   DevBuf *bufs[] = {&ctx->arenas, &ctx->seqs, &ctx->offs, &ctx->order, &ctx->subset, &ctx->idx,
+                    &ctx->states, &ctx->tasks, &ctx->scratch, &ctx->small,
                     &ctx->big, &ctx->ordered, &ctx->scan, &ctx->evalbuf};
   for (DevBuf *b : bufs)
     if (b->p) cudaFree(b->p);
@@ -362,6 +460,10 @@ int rafft_create(rafft_ctx **out, int cuda_device, const rafft_energy_params *ep
     if (s) { int v = atoi(s); if (v >= 32 && v <= RF_BLOCK_THREADS_MAX && v % 32 == 0) ctx->block_threads = v; }
     s = getenv("RAFFT_BLOCKS_PER_SM");
     if (s) { int v = atoi(s); if (v >= 1 && v <= 32) ctx->blocks_per_sm = v; }
+    s = getenv("RAFFT_MAX_WAVE");
+    if (s) { long v = atol(s); if (v >= 1) ctx->max_wave = v; }
+    s = getenv("RAFFT_MAX_TASKS");
+    if (s) { long v = atol(s); if (v >= 1) ctx->max_tasks = v; }
     return RAFFT_OK;
   }();
   free(D);
@@ -485,21 +587,30 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
       ctx->big = nb;
     }
     O = N;
-    /* arenas: as many resident blocks as the launch can use, within the memory budget */
+    /* queue of this retry round: the m sequences, longest first */
+    const int32_t *d_subset = nullptr;
+    if (round > 0) {
+      CK(cudaMemcpyAsync(ctx->subset.p, todo.data(), sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, ctx->stream));
+      h2d_bytes += sizeof(int32_t) * (int64_t)m;
+      d_subset = (const int32_t *)ctx->subset.p;
+    }
+    /* waves: as many sequences at once as the memory budget allows (one arena each) */
     size_t free_b = 0, total_b = 0;
     CK(cudaMemGetInfo(&free_b, &total_b));
-    int64_t grid = std::min<int64_t>(m, (int64_t)ctx->sm_count * ctx->blocks_per_sm);
-    int64_t budget = (int64_t)((free_b + ctx->arenas.cap) * 0.6);
-    if (grid * caps.arena_bytes > budget) grid = std::max<int64_t>(1, budget / caps.arena_bytes);
+    int64_t budget = (int64_t)((free_b + ctx->arenas.cap + ctx->scratch.cap) * 0.7);
+    int64_t wave = std::min<int64_t>(m, std::max<int64_t>(1, (budget * 3 / 4) / caps.arena_bytes));
+    if (ctx->max_wave > 0) wave = std::min<int64_t>(wave, ctx->max_wave);
+    int64_t qcap = std::min<int64_t>(wave * 64, std::max<int64_t>(64, (budget / 4) / caps.wscratch_bytes));
+    if (ctx->max_tasks > 0) qcap = std::min<int64_t>(qcap, ctx->max_tasks);
     {
       /* The hash tables at the head of every arena must be empty before a run; a run leaves
        * them empty again, so they are zeroed only when the buffer or its layout changes. */
       void *before = ctx->arenas.p;
-      if (int rc = dev_reserve(ctx, ctx->arenas, (size_t)(grid * caps.arena_bytes))) return fail(rc);
+      if (int rc = dev_reserve(ctx, ctx->arenas, (size_t)(wave * caps.arena_bytes))) return fail(rc);
       uint64_t sig = 1469598103934665603ULL;
       const unsigned char *cb = (const unsigned char *)&caps;
       for (size_t k = 0; k < sizeof caps; k++) sig = (sig ^ cb[k]) * 1099511628211ULL;
-      const size_t need = (size_t)(grid * caps.arena_bytes);
+      const size_t need = (size_t)(wave * caps.arena_bytes);
       if (before != ctx->arenas.p || sig != ctx->arena_sig || ctx->arena_dirty) {
         CK(cudaMemsetAsync(ctx->arenas.p, 0, need, ctx->stream));
         ctx->arena_sig = sig;
@@ -510,21 +621,53 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
         ctx->arena_clean = need;
       }
     }
-    /* queue */
-    const int32_t *d_subset = nullptr;
-    if (round > 0) {
-      CK(cudaMemcpyAsync(ctx->subset.p, todo.data(), sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, ctx->stream));
-      h2d_bytes += sizeof(int32_t) * (int64_t)m;
-      d_subset = (const int32_t *)ctx->subset.p;
-      /* reset the queue head only */
-      CK(cudaMemsetAsync(&O.cursors[4], 0, sizeof(unsigned long long), ctx->stream));
-    }
+    if (int rc = dev_reserve(ctx, ctx->states, sizeof(SeqState) * (size_t)wave)) return fail(rc);
+    if (int rc = dev_reserve(ctx, ctx->tasks, sizeof(int32_t) * 2 * (size_t)qcap)) return fail(rc);
+    if (int rc = dev_reserve(ctx, ctx->scratch, (size_t)qcap * (size_t)caps.wscratch_bytes)) return fail(rc);
+    if (int rc = dev_reserve(ctx, ctx->small, 256)) return fail(rc);
+    WaveCtx wc;
+    memset(&wc, 0, sizeof wc);
+    wc.E = ctx->d_energy; wc.prm = F; wc.caps = caps;
+    arena_offsets(wc.aoff, caps, F);
+    wc.arenas = (char *)ctx->arenas.p; wc.states = (SeqState *)ctx->states.p;
+    wc.seqs = d_seqs; wc.offs = d_offs;
+    wc.Q.n_tasks = (int32_t *)ctx->small.p; wc.Q.cap = (int32_t)qcap; wc.Q.task = (int32_t *)ctx->tasks.p;
+    wc.Q.scratch = (char *)ctx->scratch.p; wc.Q.self = 0;
+    wc.n_active = (int32_t *)ctx->small.p + 1;
+    wc.out = O;
+    const int egrid = ctx->sm_count * ctx->blocks_per_sm;
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
     order_kernel<<<(m + 255) / 256, 256, 0, ctx->stream>>>(d_offs, d_subset, m, (int32_t *)ctx->order.p);
-    fold_kernel<<<(unsigned)grid, T, 0, ctx->stream>>>(ctx->d_energy, F, caps, (char *)ctx->arenas.p, d_seqs,
-                                                      d_offs, (const int32_t *)ctx->order.p, m, O);
+    launches++;
+    for (int64_t w0 = 0; w0 < m; w0 += wave) {
+      const int nw = (int)std::min<int64_t>(wave, m - w0);
+      wc.order = (const int32_t *)ctx->order.p + w0;
+      wc.n = nw;
+      k_init<<<nw, T, 0, ctx->stream>>>(wc);
+      launches++;
+      for (int it = 0;; it++) {
+        CK(cudaMemsetAsync(ctx->small.p, 0, 8, ctx->stream));
+        k_gather<<<nw, T, 0, ctx->stream>>>(wc);
+        k_expand<1><<<egrid, 128, 0, ctx->stream>>>(wc);
+        k_expand<2><<<egrid, 128, 0, ctx->stream>>>(wc);
+        k_expand<3><<<egrid, 128, 0, ctx->stream>>>(wc);
+        k_expand<4><<<egrid, 128, 0, ctx->stream>>>(wc);
+        k_expand<5><<<egrid, 128, 0, ctx->stream>>>(wc);
+        k_combine<<<nw, T, 0, ctx->stream>>>(wc);
+        k_select<<<nw, T, 0, ctx->stream>>>(wc);
+        k_materialise<<<nw, T, 0, ctx->stream>>>(wc);
+        launches += 9;
+        CK(cudaMemcpyAsync(ctx->h_small + 16, (int32_t *)ctx->small.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        d2h += 8;
+        const int32_t *hs = (const int32_t *)(ctx->h_small + 16);
+        if (hs[1] == 0) break;
+        if (it > 100000) { ctx->err = "rafft_fold_batch: no progress"; return fail(RAFFT_ERR_CUDA); }
+      }
+      k_finish<<<nw, T, 0, ctx->stream>>>(wc);
+      launches++;
+    }
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
-    launches += 2;
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(h_status.data(), O.status, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaMemcpyAsync(ctx->h_small, O.cursors, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));

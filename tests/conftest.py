@@ -104,9 +104,11 @@ def emu():
                            C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
     L.emu_fold.restype = C.c_int
     L.emu_free.argtypes = [C.c_void_p]
+    L.emu_set_queue_cap.argtypes = [C.c_int]
 
-    def fold(seq, reverse=0, nthreads=32, scale=1, **kw):
+    def fold(seq, reverse=0, nthreads=32, scale=1, queue_cap=0, **kw):
         import pyoracle
+        L.emu_set_queue_cap(queue_cap)
         p = dict(nb_mode=100, max_stack=1, max_branch=1000, min_hp=3, min_nrj=0.0, gc=3.0, au=2.0, gu=1.0)
         p.update(kw)
         prm = Params(p["nb_mode"], p["max_stack"], p["max_branch"], p["min_hp"], 1, p["min_nrj"], 37.0,

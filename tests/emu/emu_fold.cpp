@@ -13,7 +13,11 @@
 
 using namespace rafft;
 
+static int g_queue_cap = 0;
+
 extern "C" {
+
+void emu_set_queue_cap(int cap) { g_queue_cap = cap; }
 
 void emu_default_energy_params(rafft_energy_params *ep) { default_energy_params(ep); }
 
@@ -35,11 +39,18 @@ int emu_fold(const rafft_energy_params *ep_in, const char *seq, int L, const raf
   Exec::emu_threads() = nthreads > 0 ? nthreads : 32;
   Caps caps = make_caps(L, F, Exec::nthreads(), scale > 0 ? scale : 1);
   std::vector<char> arena((size_t)caps.arena_bytes, 0);  /* hash tables start empty */
-  Fold f;
-  f.E = D; f.prm = F; f.caps = caps;
-  arena_carve(f.A, arena.data(), caps, F);
-  BlockShared sh;
+  Fold f(D, F, caps);
+  ArenaOff aoff;
+  arena_offsets(aoff, caps, F);
+  arena_bind(f.A, arena.data(), aoff);
+  SeqState sh;
   f.sh = &sh;
+  /* region-expansion work list of one round (tiny capacities exercise the deferral path) */
+  int qcap = g_queue_cap > 0 ? g_queue_cap : caps.todo_cap;
+  int32_t n_tasks = 0;
+  std::vector<int32_t> tasks(2 * (size_t)qcap);
+  std::vector<char> scratch((size_t)caps.wscratch_bytes);
+  f.Q.n_tasks = &n_tasks; f.Q.cap = qcap; f.Q.task = tasks.data(); f.Q.scratch = scratch.data(); f.Q.self = 0;
   /* output for one sequence */
   int64_t scap = (int64_t)caps.store_cap, ecap = (int64_t)caps.step_cap * F.max_stack;
   std::vector<int32_t> status(1), nstruct(1), nstep(1), energy(scap), step_n(caps.step_cap), entries(ecap);
@@ -52,7 +63,22 @@ int emu_fold(const rafft_energy_params *ep_in, const char *seq, int L, const raf
   out.seq_entry = sentry.data(); out.counters = counters.data(); out.energy = energy.data();
   out.db = db.data(); out.step_n = step_n.data(); out.entries = entries.data(); out.cursors = cursors;
   out.struct_cap = scap; out.db_cap = (int64_t)db.size(); out.step_cap = caps.step_cap; out.entry_cap = ecap;
-  f.run(seq, L, 0, out);
+  /* the host loop of rafft_cuda.cu, for one sequence: rounds of phase "kernels" */
+  f.phase_init(seq, L, 0);
+  for (int round = 0; sh.active; round++) {
+    n_tasks = 0;
+    f.phase_gather();
+    int nt = n_tasks < qcap ? n_tasks : qcap;
+    for (int t = 0; t < nt; t++) {
+      int a = Exec::order() ? nt - 1 - t : t;
+      f.expand_node(tasks[2 * a + 1], scratch.data());
+    }
+    f.phase_combine();
+    f.phase_select();
+    f.phase_materialise();
+    if (round > 100000) { fprintf(stderr, "emu_fold: no progress\n"); return -3; }
+  }
+  f.phase_finish(out);
   /* run() must leave the hash tables empty for the next sequence of the arena */
   {
     size_t tb = arena_table_bytes(caps);

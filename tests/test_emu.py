@@ -57,3 +57,13 @@ def test_emu_capacity_is_reported_not_silent(emu):
 def test_emu_invalid_letter(emu):
     rc, steps, _, _ = emu("GGGANACCC", nb_mode=10, max_stack=2)
     assert rc == 2  # RAFFT_ERR_SEQ (reference: KeyError, rafft/utils.py:73-80)
+
+
+def test_emu_task_queue_overflow_defers(emu, oracle):
+    "a full expansion work list defers regions to the next round without changing the result"
+    for k, cap in enumerate((1, 2, 5)):
+        seq = splitmix_seq(600 + k, 90)
+        rc, steps, cnt, _ = emu(seq, queue_cap=cap, nb_mode=50, max_stack=10)
+        want, wcnt = oracle.fold(seq, 50, 10, 1000, counters=True)
+        assert rc == 0 and steps == want
+        assert cnt[:5] == wcnt[:5]
