@@ -51,6 +51,8 @@ struct DevEnergy {
   uint32_t tri_key[64], tetra_key[64], hexa_key[64]; /* 2 bits per base, first base highest */
   int32_t tri_e[64], tetra_e[64], hexa_e[64];
   int32_t logterm[4096]; /* (int)(lxc*log(u/30)) for u > 30, host libm (bit-equal to oracle) */
+  /* membership bitmaps of the special-hairpin keys (bit = key): most hairpins are not special */
+  uint32_t tri_bm[32], tetra_bm[128], hexa_bm[2048];
 };
 
 /* Launch-wide constants. */
@@ -317,14 +319,17 @@ RF_NOINLINE int e_hairpin(const EnergyView &ev, int i, int j) {
     uint32_t key = 0;
     for (int k = i; k <= j; k++) key = (key << 2) | ev.s[k];
     if (u == 4) {
-      for (int k = 0; k < P->n_tetra; k++)
-        if (P->tetra_key[k] == key) return P->tetra_e[k];
+      if ((P->tetra_bm[key >> 5] >> (key & 31)) & 1)
+        for (int k = 0; k < P->n_tetra; k++)
+          if (P->tetra_key[k] == key) return P->tetra_e[k];
     } else if (u == 6) {
-      for (int k = 0; k < P->n_hexa; k++)
-        if (P->hexa_key[k] == key) return P->hexa_e[k];
+      if ((P->hexa_bm[key >> 5] >> (key & 31)) & 1)
+        for (int k = 0; k < P->n_hexa; k++)
+          if (P->hexa_key[k] == key) return P->hexa_e[k];
     } else {
-      for (int k = 0; k < P->n_tri; k++)
-        if (P->tri_key[k] == key) return P->tri_e[k];
+      if ((P->tri_bm[key >> 5] >> (key & 31)) & 1)
+        for (int k = 0; k < P->n_tri; k++)
+          if (P->tri_key[k] == key) return P->tri_e[k];
       return e + (t > 1 ? P->terminal_au : 0);
     }
   }
@@ -478,12 +483,18 @@ struct SeqState {
 typedef SeqState BlockShared;
 
 /* Region-expansion work list of one round: (sequence slot, node id) + one scratch slot each. */
+#define RF_FAST_CLASSES 6
 struct TaskQueue {
   int32_t *n_tasks;   /* device counter; may overshoot cap */
   int32_t cap;
   int32_t *task;      /* 2 ints per task */
   char *scratch;      /* cap * caps.wscratch_bytes */
   int32_t self;       /* slot of the sequence this Fold works on (block scope) */
+  /* second list: regions small enough for the shared-memory expansion (expand_fast.cuh);
+   * fast_cap == 0 (host emulation) sends everything to the first list */
+  int32_t *n_fast;    /* RF_FAST_CLASSES counters: one list per size class (32 << class lags) */
+  int32_t fast_cap, fast_lv, fast_br;
+  int32_t *fast_task; /* RF_FAST_CLASSES lists of fast_cap tasks, 2 ints per task */
 };
 
 RF_HD size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
@@ -1116,8 +1127,13 @@ struct Fold {
         for (int k = 0; k < S.nl_n; k++) {
           int v = A.nlist[S.nl_off + k];
           if (A.node[v].cand_n == -1 && Exec::atomic_cas(&A.node[v].cand_n, -1, -2) == -1) {
-            int at = Exec::atomic_add(Q.n_tasks, 1);
-            if (at < Q.cap) { Q.task[2 * at] = Q.self; Q.task[2 * at + 1] = v; }
+            const bool fast = Q.fast_cap > 0 && A.node[v].lv <= Q.fast_lv && A.node[v].br_n <= Q.fast_br;
+            int cls = 0;
+            while ((32 << cls) < 2 * A.node[v].lv - 1) cls++;
+            int32_t *list = fast ? Q.fast_task + 2 * (size_t)cls * (size_t)Q.fast_cap : Q.task;
+            const int cap = fast ? Q.fast_cap : Q.cap;
+            int at = Exec::atomic_add(fast ? Q.n_fast + cls : Q.n_tasks, 1);
+            if (at < cap) { list[2 * at] = Q.self; list[2 * at + 1] = v; }
             else { A.node[v].cand_n = -1; sh->expand_pending = 1; } /* next round */
           }
         }

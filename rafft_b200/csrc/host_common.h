@@ -94,6 +94,9 @@ inline bool build_dev_energy(const rafft_energy_params *ep, DevEnergy *D, std::s
   for (int i = 0; i < ep->n_tri; i++) { if (!key(ep->tri[i], 5, D->tri_key[i])) { err = "bad triloop"; return false; } D->tri_e[i] = ep->tri_e[i]; }
   for (int i = 0; i < ep->n_tetra; i++) { if (!key(ep->tetra[i], 6, D->tetra_key[i])) { err = "bad tetraloop"; return false; } D->tetra_e[i] = ep->tetra_e[i]; }
   for (int i = 0; i < ep->n_hexa; i++) { if (!key(ep->hexa[i], 8, D->hexa_key[i])) { err = "bad hexaloop"; return false; } D->hexa_e[i] = ep->hexa_e[i]; }
+  for (int i = 0; i < ep->n_tri; i++) D->tri_bm[D->tri_key[i] >> 5] |= 1u << (D->tri_key[i] & 31);
+  for (int i = 0; i < ep->n_tetra; i++) D->tetra_bm[D->tetra_key[i] >> 5] |= 1u << (D->tetra_key[i] & 31);
+  for (int i = 0; i < ep->n_hexa; i++) D->hexa_bm[D->hexa_key[i] >> 5] |= 1u << (D->hexa_key[i] & 31);
   for (int u = 0; u < 4096; u++) D->logterm[u] = u > 30 ? (int)(ep->lxc * log((double)u / 30.0)) : 0;
   return true;
 }

@@ -19,6 +19,7 @@
 #include <string>
 #include <vector>
 #include "host_common.h"
+#include "expand_fast.cuh"
 
 using namespace rafft;
 
@@ -61,6 +62,8 @@ struct WaveCtx {
   const int32_t *order;
   int32_t n;
   TaskQueue Q;
+  FastCfg fast;
+  int32_t *fast_next; /* dynamic work counter of k_expand_fast */
   int32_t *n_active;
   OutBuf out;
 };
@@ -164,6 +167,67 @@ __global__ void __launch_bounds__(128) k_expand(RF_WAVE_PARAM) {
     if (PHASE == 5) f.expand_e5(n, W);
   }
 }
+
+/* shared-memory expansion: one warp per region; the warps of a block take RF_FAST_WARPS regions of
+ * one size class at a time and walk through the phases together (block barriers), so that an SM
+ * executes one phase at a time and its code stays in the instruction caches. */
+template <int K>
+__device__ __forceinline__ void fast_class(const WaveCtx &c, int cls, char *ws, int *s_base) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int nt = min(c.Q.n_fast[cls], c.Q.fast_cap);
+  const int32_t *list = c.Q.fast_task + 2 * (size_t)cls * (size_t)c.Q.fast_cap;
+  for (;;) {
+    __syncthreads();
+    if (threadIdx.x == 0) *s_base = atomicAdd(c.fast_next + cls, nwarps);
+    __syncthreads();
+    const int base = *s_base;
+    if (base >= nt) break;
+    const int t = base + warp;
+    const bool has = t < nt;
+    int j = 0, v = 0;
+    if (has) { j = list[2 * t]; v = list[2 * t + 1]; }
+    char *arena = c.arenas + (size_t)j * (size_t)c.caps.arena_bytes;
+    SeqState *st = c.states + j;
+#define RF_FAST_CALL c.E, c.prm, c.caps, c.fast, arena, c.aoff, st, v, ws, lane
+    if (has) fast_p1(RF_FAST_CALL);
+    __syncthreads();
+    if (has) fast_p2(RF_FAST_CALL);
+    __syncthreads();
+    if (has) fast_p3(RF_FAST_CALL, 32 * K);
+    __syncthreads();
+    if (has) fast_p4<K>(RF_FAST_CALL);
+    __syncthreads();
+    if (has) fast_p5(RF_FAST_CALL);
+    __syncthreads();
+    if (has) fast_p6(RF_FAST_CALL);
+    __syncthreads();
+    if (has) fast_p7(RF_FAST_CALL);
+#undef RF_FAST_CALL
+  }
+}
+
+template <int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_expand_fast(RF_WAVE_PARAM) {
+  extern __shared__ __align__(16) char fast_smem[];
+  __shared__ int s_base;
+  char *ws = fast_smem + (size_t)(threadIdx.x >> 5) * (size_t)c.fast.smem_per_warp;
+  /* largest regions first */
+  fast_class<32>(c, 5, ws, &s_base);
+  fast_class<16>(c, 4, ws, &s_base);
+  fast_class<8>(c, 3, ws, &s_base);
+  fast_class<4>(c, 2, ws, &s_base);
+  fast_class<2>(c, 1, ws, &s_base);
+  fast_class<1>(c, 0, ws, &s_base);
+}
+
+/* launch shapes of k_expand_fast: (threads per block, blocks per SM) */
+typedef void (*fast_kernel_t)(const WaveCtx);
+struct FastShape { int threads, blocks; fast_kernel_t fn; };
+static const FastShape g_fast_shapes[] = {
+    {512, 1, k_expand_fast<512, 1>}, {256, 2, k_expand_fast<256, 2>}, {256, 3, k_expand_fast<256, 3>},
+    {128, 4, k_expand_fast<128, 4>}, {128, 6, k_expand_fast<128, 6>}, {384, 2, k_expand_fast<384, 2>},
+    {768, 1, k_expand_fast<768, 1>}, {128, 5, k_expand_fast<128, 5>}, {64, 8, k_expand_fast<64, 8>},
+    {64, 12, k_expand_fast<64, 12>}};
 
 /* One block.  Ordered offsets: struct_off/db_off/step_off (n+1 each) and the per-sequence
  * base of its entries, ent_base (n+1); totals[0..3] = structures, db bytes, steps, entries. */
@@ -322,13 +386,15 @@ struct rafft_ctx {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   DevEnergy *d_energy = nullptr;
-  DevBuf arenas, seqs, offs, order, subset, idx, big, ordered, scan, evalbuf, states, tasks, scratch, small;
+  DevBuf arenas, seqs, offs, order, subset, idx, big, ordered, scan, evalbuf, states, tasks, ftasks, scratch, small;
   std::vector<HostBlock> pinned_free;
   int64_t *h_small = nullptr; /* pinned: totals + cursors */
   int block_threads = 64;   /* threads per block of the block-scope phase kernels */
   int blocks_per_sm = 16;   /* grid of the warp-task kernels: blocks per SM */
   int64_t max_wave = 0;     /* sequences folded together (0 = as many as memory allows) */
   int64_t max_tasks = 0;    /* capacity of the region work list (0 = automatic) */
+  int fast_shape = 2;       /* index into g_fast_shapes (RAFFT_FAST_SHAPE) */
+  int use_fast = 1;         /* shared-memory expansion for small regions (RAFFT_FAST=0 disables) */
   uint64_t arena_sig = 0;   /* layout of the arenas whose hash tables are known to be empty */
   bool arena_dirty = true;
   size_t arena_clean = 0;   /* leading bytes of the arena buffer known to be clean */
@@ -404,7 +470,7 @@ void rafft_destroy(rafft_ctx *ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   DevBuf *bufs[] = {&ctx->arenas, &ctx->seqs, &ctx->offs, &ctx->order, &ctx->subset, &ctx->idx,
-                    &ctx->states, &ctx->tasks, &ctx->scratch, &ctx->small,
+                    &ctx->states, &ctx->tasks, &ctx->ftasks, &ctx->scratch, &ctx->small,
                     &ctx->big, &ctx->ordered, &ctx->scan, &ctx->evalbuf};
   for (DevBuf *b : bufs)
     if (b->p) cudaFree(b->p);
@@ -462,6 +528,10 @@ int rafft_create(rafft_ctx **out, int cuda_device, const rafft_energy_params *ep
     if (s) { int v = atoi(s); if (v >= 1 && v <= 32) ctx->blocks_per_sm = v; }
     s = getenv("RAFFT_MAX_WAVE");
     if (s) { long v = atol(s); if (v >= 1) ctx->max_wave = v; }
+    s = getenv("RAFFT_FAST_SHAPE");
+    if (s) { int v = atoi(s); if (v >= 0 && v < (int)(sizeof g_fast_shapes / sizeof g_fast_shapes[0])) ctx->fast_shape = v; }
+    s = getenv("RAFFT_FAST");
+    if (s) ctx->use_fast = atoi(s) != 0;
     s = getenv("RAFFT_MAX_TASKS");
     if (s) { long v = atol(s); if (v >= 1) ctx->max_tasks = v; }
     return RAFFT_OK;
@@ -601,7 +671,17 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     int64_t wave = std::min<int64_t>(m, std::max<int64_t>(1, (budget * 3 / 4) / caps.arena_bytes));
     if (ctx->max_wave > 0) wave = std::min<int64_t>(wave, ctx->max_wave);
     int64_t qcap = std::min<int64_t>(wave * 64, std::max<int64_t>(64, (budget / 4) / caps.wscratch_bytes));
-    if (ctx->max_tasks > 0) qcap = std::min<int64_t>(qcap, ctx->max_tasks);
+    /* regions of up to 512 positions take the shared-memory expansion (expand_fast.cuh); only
+     * longer ones need a global scratch slot */
+    FastCfg fastcfg;
+    int64_t fcap = 0;
+    if (ctx->use_fast && build_fast_cfg(fastcfg, Lr, F)) {
+      fcap = wave * std::max<int64_t>(128, 4 * (int64_t)F.max_stack);
+      qcap = std::min<int64_t>(qcap, wave * 8 + 1024);
+    } else {
+      memset(&fastcfg, 0, sizeof fastcfg);
+    }
+    if (ctx->max_tasks > 0) { qcap = std::min<int64_t>(qcap, ctx->max_tasks); fcap = std::min<int64_t>(fcap, ctx->max_tasks); }
     {
       /* The hash tables at the head of every arena must be empty before a run; a run leaves
        * them empty again, so they are zeroed only when the buffer or its layout changes. */
@@ -623,6 +703,7 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     }
     if (int rc = dev_reserve(ctx, ctx->states, sizeof(SeqState) * (size_t)wave)) return fail(rc);
     if (int rc = dev_reserve(ctx, ctx->tasks, sizeof(int32_t) * 2 * (size_t)qcap)) return fail(rc);
+    if (int rc = dev_reserve(ctx, ctx->ftasks, sizeof(int32_t) * 2 * RF_FAST_CLASSES * (size_t)(fcap + 1))) return fail(rc);
     if (int rc = dev_reserve(ctx, ctx->scratch, (size_t)qcap * (size_t)caps.wscratch_bytes)) return fail(rc);
     if (int rc = dev_reserve(ctx, ctx->small, 256)) return fail(rc);
     WaveCtx wc;
@@ -634,8 +715,16 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     wc.Q.n_tasks = (int32_t *)ctx->small.p; wc.Q.cap = (int32_t)qcap; wc.Q.task = (int32_t *)ctx->tasks.p;
     wc.Q.scratch = (char *)ctx->scratch.p; wc.Q.self = 0;
     wc.n_active = (int32_t *)ctx->small.p + 1;
+    wc.Q.n_fast = (int32_t *)ctx->small.p + 2; wc.Q.fast_cap = (int32_t)fcap; wc.Q.fast_task = (int32_t *)ctx->ftasks.p;
+    wc.Q.fast_lv = fastcfg.L_cap; wc.Q.fast_br = fastcfg.br_cap;
+    wc.fast = fastcfg;
+    wc.fast_next = (int32_t *)ctx->small.p + 2 + RF_FAST_CLASSES;
+    const FastShape &fsh = g_fast_shapes[ctx->fast_shape];
+    const size_t fast_smem = (size_t)(fsh.threads / 32) * (size_t)fastcfg.smem_per_warp;
+    const bool any_generic = fcap == 0 || Lr > fastcfg.L_cap || Lr / 2 > fastcfg.br_cap;
     wc.out = O;
     const int egrid = ctx->sm_count * ctx->blocks_per_sm;
+    if (fcap > 0) CK(cudaFuncSetAttribute(fsh.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast_smem));
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
     order_kernel<<<(m + 255) / 256, 256, 0, ctx->stream>>>(d_offs, d_subset, m, (int32_t *)ctx->order.p);
     launches++;
@@ -646,17 +735,25 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
       k_init<<<nw, T, 0, ctx->stream>>>(wc);
       launches++;
       for (int it = 0;; it++) {
-        CK(cudaMemsetAsync(ctx->small.p, 0, 8, ctx->stream));
+        CK(cudaMemsetAsync(ctx->small.p, 0, 64, ctx->stream));
         k_gather<<<nw, T, 0, ctx->stream>>>(wc);
-        k_expand<1><<<egrid, 128, 0, ctx->stream>>>(wc);
-        k_expand<2><<<egrid, 128, 0, ctx->stream>>>(wc);
-        k_expand<3><<<egrid, 128, 0, ctx->stream>>>(wc);
-        k_expand<4><<<egrid, 128, 0, ctx->stream>>>(wc);
-        k_expand<5><<<egrid, 128, 0, ctx->stream>>>(wc);
+        launches++;
+        if (fcap > 0) {
+          fsh.fn<<<ctx->sm_count * fsh.blocks, fsh.threads, fast_smem, ctx->stream>>>(wc);
+          launches++;
+        }
+        if (any_generic) {
+          k_expand<1><<<egrid, 128, 0, ctx->stream>>>(wc);
+          k_expand<2><<<egrid, 128, 0, ctx->stream>>>(wc);
+          k_expand<3><<<egrid, 128, 0, ctx->stream>>>(wc);
+          k_expand<4><<<egrid, 128, 0, ctx->stream>>>(wc);
+          k_expand<5><<<egrid, 128, 0, ctx->stream>>>(wc);
+          launches += 5;
+        }
         k_combine<<<nw, T, 0, ctx->stream>>>(wc);
         k_select<<<nw, T, 0, ctx->stream>>>(wc);
         k_materialise<<<nw, T, 0, ctx->stream>>>(wc);
-        launches += 9;
+        launches += 3;
         CK(cudaMemcpyAsync(ctx->h_small + 16, (int32_t *)ctx->small.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
         CK(cudaStreamSynchronize(ctx->stream));
         d2h += 8;

@@ -16,6 +16,8 @@ subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(lib)], cwd=tmp, cap
 cubin = [f for f in os.listdir(tmp) if f.endswith(".cubin")][0]
 dis = subprocess.run(["nvdisasm", "-gi", "-c", os.path.join(tmp, cubin)], capture_output=True, text=True).stdout
 insts, cur, insec = [], None, False
+group, fresh = [], True
+INNER = os.environ.get('NCU_LINES_INNER', '0') == '1'
 for line in dis.splitlines():
     m = re.match(r"\s*\.section\s+\.text\.(\S+?),", line)
     if m:
@@ -25,11 +27,18 @@ for line in dis.splitlines():
         continue
     m = re.search(r'//## File "([^"]+)", line (\d+)', line)
     if m:
-        cur = (os.path.basename(m.group(1)), int(m.group(2)))
+        if fresh:
+            group = []; fresh = False
+        group.append((os.path.basename(m.group(1)), int(m.group(2))))
+        cur = group[-1]
         continue
     m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(.*?);", line)
     if m:
-        insts.append((cur, m.group(2).strip()))
+        fresh = True
+        pick = cur
+        if INNER:  # innermost line that lies in this repository's sources
+            pick = next((g for g in group if not g[0].endswith((".hpp", ".h"))), cur)
+        insts.append((pick, m.group(2).strip()))
 print("sass rows: ncu %d, nvdisasm %d" % (len(data), len(insts)))
 n = min(len(data), len(insts))
 mism = sum(1 for k in range(n) if data[k]["Source"].split()[0].lstrip("@!P0123456789T ") [:3] != insts[k][1].split()[0].lstrip("@!P0123456789T ")[:3])
