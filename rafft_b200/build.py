@@ -13,7 +13,7 @@ SOURCES = ["rafft_cuda.cu"]
 DEPS = ["rafft_cuda.cu", "fold_core.cuh", "host_common.h", "turner2004.inc",
         os.path.join("..", "..", "include", "rafft_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-              "-shared", "-Xcompiler", "-fPIC", "-diag-suppress", "177"]
+              "-shared", "-Xcompiler", "-fPIC", "-diag-suppress", "177,550"]
 
 
 def nvcc_path():

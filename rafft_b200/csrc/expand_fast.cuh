@@ -60,7 +60,7 @@ inline bool build_fast_cfg(FastCfg &fc, int L_max, const FoldParams &F) {
   const int ck_cap = fast_pow2(nr);
   size_t off = 0;
   auto carve = [&](size_t bytes) { off = (off + 15) / 16 * 16; size_t o = off; off += bytes; return (int32_t)o; };
-  fc.o_mask = carve(4 * 10 * (size_t)fc.mws);
+  fc.o_mask = carve(4 * 6 * (size_t)fc.mws);
   fc.o_pos = carve(2 * (size_t)fc.L_cap);
   fc.o_brcnt = carve((size_t)fc.L_cap);
   fc.o_lcode = carve((size_t)fc.L_cap);
@@ -82,44 +82,48 @@ inline bool build_fast_cfg(FastCfg &fc, int L_max, const FoldParams &F) {
 
 #ifdef __CUDACC__
 
-/* Bitonic sort, descending, of 32*K 32-bit keys held K per lane (key index = 32*r + lane). */
+/* Bitonic sort, descending, of 32*K 32-bit keys held K per lane in BLOCKED layout (key index =
+ * K*lane + r): the stages with distance j < K are compare-exchanges between registers of one
+ * lane (2 instructions per key), only j >= K needs a shuffle -- half as many shuffle stages as
+ * the strided layout. */
 template <int K, int J>
-__device__ __forceinline__ void fast_inlane(uint32_t (&v)[K], int kbits /* k >> 5 */) {
+__device__ __forceinline__ void fast_inlane(uint32_t (&v)[K], int k, int lane) {
 #pragma unroll
   for (int r = 0; r < K; r++) {
     if ((r & J) == 0 && (r | J) < K) {
       const uint32_t a = v[r], b = v[r | J];
       const uint32_t hi = max(a, b), lo = min(a, b);
-      const bool desc = (r & kbits) == 0;
+      const bool desc = ((K * lane + r) & k) == 0;
       v[r] = desc ? hi : lo;
       v[r | J] = desc ? lo : hi;
     }
   }
 }
 
-/* keys a[32*r + lane] -> registers, sorted descending across the warp */
+/* keys a[32*r + lane] (any input order will do) -> registers, sorted descending: afterwards
+ * rank t is register t % K of lane t / K */
 template <int K>
 __device__ __forceinline__ void fast_sort_regs(const uint32_t *a, uint32_t (&v)[K], int lane) {
 #pragma unroll
   for (int r = 0; r < K; r++) v[r] = a[32 * r + lane];
   for (int k = 2; k <= 32 * K; k <<= 1) {
     for (int j = k >> 1; j > 0; j >>= 1) {
-      if (j >= 32) {
-        const int kb = k >> 5;
-        switch (j >> 5) {
-          case 1: fast_inlane<K, 1>(v, kb); break;
-          case 2: fast_inlane<K, 2>(v, kb); break;
-          case 4: fast_inlane<K, 4>(v, kb); break;
-          case 8: fast_inlane<K, 8>(v, kb); break;
-          default: fast_inlane<K, 16>(v, kb); break;
+      if (j < K) {
+        switch (j) {
+          case 1: fast_inlane<K, 1>(v, k, lane); break;
+          case 2: fast_inlane<K, 2>(v, k, lane); break;
+          case 4: fast_inlane<K, 4>(v, k, lane); break;
+          case 8: fast_inlane<K, 8>(v, k, lane); break;
+          default: fast_inlane<K, 16>(v, k, lane); break;
         }
       } else {
-        const bool lower = (lane & j) == 0;
+        /* k > j >= K: the direction of the run and the side of the pair depend on the lane only */
+        const int jl = j / K;
+        const bool keepmax = ((lane & jl) == 0) == (((K * lane) & k) == 0);
 #pragma unroll
         for (int r = 0; r < K; r++) {
-          const uint32_t o = __shfl_xor_sync(0xffffffffu, v[r], j);
-          const bool desc = ((32 * r + lane) & k) == 0;
-          v[r] = (lower == desc) ? max(v[r], o) : min(v[r], o);
+          const uint32_t o = __shfl_xor_sync(0xffffffffu, v[r], jl);
+          v[r] = keepmax ? max(v[r], o) : min(v[r], o);
         }
       }
     }
@@ -130,8 +134,9 @@ template <int K>
 __device__ __noinline__ void fast_sort_desc(uint32_t *a, int lane) {
   uint32_t v[K];
   fast_sort_regs<K>(a, v, lane);
+  __syncwarp();
 #pragma unroll
-  for (int r = 0; r < K; r++) a[32 * r + lane] = v[r];
+  for (int r = 0; r < K; r++) a[K * lane + r] = v[r];
 }
 
 __device__ __forceinline__ void fast_sort_dispatch(uint32_t *a, int n /* power of two >= 32 */, int lane) {
@@ -226,7 +231,8 @@ __device__ __forceinline__ int fast_stem_dE(const FastTask &T, const EnergyView 
   const int ci = n.ci, cj = n.cj, m = n.br_n, lv = n.lv;                                        \
   const int MWS = fc.mws;                                                                       \
   uint32_t *mask = (uint32_t *)(ws + fc.o_mask) + 1; /* word -1 is the zero pad */              \
-  uint32_t *F = mask, *R = mask + 4 * MWS, *CL = mask + 8 * MWS, *CLR = mask + 9 * MWS;         \
+  uint32_t *FH = mask, *FL = mask + MWS, *RH = mask + 2 * MWS, *RL = mask + 3 * MWS,            \
+           *CL = mask + 4 * MWS, *CLR = mask + 5 * MWS;                                         \
   uint16_t *pos = (uint16_t *)(ws + fc.o_pos);                                                  \
   uint8_t *brcnt = (uint8_t *)(ws + fc.o_brcnt);                                                \
   uint8_t *lcode = (uint8_t *)(ws + fc.o_lcode);                                                \
@@ -240,7 +246,7 @@ __device__ __forceinline__ int fast_stem_dE(const FastTask &T, const EnergyView 
   const int nlag = 2 * lv - 1;                                                                  \
   const int nr = nlag < prm.nb_mode ? nlag : prm.nb_mode;                                       \
   const unsigned FULL = 0xffffffffu;                                                            \
-  (void)code; (void)br; (void)ci; (void)cj; (void)m; (void)F; (void)R; (void)CL; (void)CLR;     \
+  (void)code; (void)br; (void)ci; (void)cj; (void)m; (void)FH; (void)FL; (void)RH; (void)RL; (void)CL; (void)CLR;     \
   (void)pos; (void)brcnt; (void)lcode; (void)pre_ml; (void)pre_ext; (void)rlag; (void)keys;     \
   (void)r_stem; (void)ck; (void)r_nb; (void)wst; (void)nr; (void)FULL;
 
@@ -291,49 +297,53 @@ __device__ __forceinline__ void fast_p1(RF_FAST_ARGS) {
   }
 }
 
-/* phase 2: one-hot masks by ballot: F_X bit t = [x_t == X], R_X bit u = [x_{lv-1-u} == X];
- *          CL bit t = position t continues t-1 in ORIGINAL coordinates, CLR its reversal */
+/* phase 2: bit-plane masks by ballot.  Base codes A,C,G,U = 0..3: FH/FL bit t = high/low bit of
+ *          x_t, RH/RL bit u = the same of x_{lv-1-u}; CL bit t = position t continues t-1 in
+ *          ORIGINAL coordinates, CLR its reversal.  With x = FH^RH', y = FL^RL' (R' = R shifted
+ *          to the lag):  G.C pairs = x&y&(FH^FL), A.U = x&y&~(FH^FL), G.U = ~x&y&FH. */
 __device__ __forceinline__ void fast_p2(RF_FAST_ARGS) {
   RF_FAST_BIND
   const int nw = (lv + 31) >> 5;
   for (int w = 0; w < nw; w++) {
     const int t = 32 * w + lane;
-    const int lc = t < lv ? lcode[t] : 8, lr = t < lv ? lcode[lv - 1 - t] : 8;
-    const unsigned f0 = __ballot_sync(FULL, (lc & 11) == 0), f1 = __ballot_sync(FULL, (lc & 11) == 1),
-                   f2 = __ballot_sync(FULL, (lc & 11) == 2), f3 = __ballot_sync(FULL, (lc & 11) == 3),
-                   fcl = __ballot_sync(FULL, (lc & 12) == 4);
-    const unsigned r0 = __ballot_sync(FULL, (lr & 11) == 0), r1 = __ballot_sync(FULL, (lr & 11) == 1),
-                   r2 = __ballot_sync(FULL, (lr & 11) == 2), r3 = __ballot_sync(FULL, (lr & 11) == 3),
-                   rcl = __ballot_sync(FULL, (lr & 12) == 4);
+    const int lc = t < lv ? lcode[t] : 0, lr = t < lv ? lcode[lv - 1 - t] : 0;
+    const unsigned fh = __ballot_sync(FULL, lc & 2), fl = __ballot_sync(FULL, lc & 1),
+                   fcl = __ballot_sync(FULL, lc & 4);
+    const unsigned rh = __ballot_sync(FULL, lr & 2), rl = __ballot_sync(FULL, lr & 1),
+                   rcl = __ballot_sync(FULL, lr & 4);
     if (lane == 0) {
-      F[w] = f0; F[MWS + w] = f1; F[2 * MWS + w] = f2; F[3 * MWS + w] = f3; CL[w] = fcl;
-      R[w] = r0; R[MWS + w] = r1; R[2 * MWS + w] = r2; R[3 * MWS + w] = r3; CLR[w] = rcl;
+      FH[w] = fh; FL[w] = fl; CL[w] = fcl; RH[w] = rh; RL[w] = rl; CLR[w] = rcl;
     }
   }
-  if (lane < 10) { mask[lane * MWS - 1] = 0; mask[lane * MWS + nw] = 0; }
+  if (lane < 6) { mask[lane * MWS - 1] = 0; mask[lane * MWS + nw] = 0; }
 }
 
 /* phase 3: correlation (utils.py:115-132): acc[p] = sum over unordered pairs i+j=p of w(x_i,x_j)
- *    = cor[p]/2 up to the common weight factor; c[p] = cor[p]/(min(p, 2lv-2-p)+1).  Two
- *    different quotients with denominators <= 512 differ by >= 2^-18, so
- *    floor(acc * 2^18 / norm) orders (and equates) them exactly as the reference's floats. */
+ *    = cor[p]/2 up to the common weight factor (only the first half of the anti-diagonal is
+ *    visited); c[p] = cor[p]/(min(p, 2lv-2-p)+1).  Two different quotients with denominators
+ *    <= 512 differ by >= 2^-18, so floor(acc * 2^18 / norm) orders (and equates) them exactly as
+ *    the reference's floats. */
 __device__ __forceinline__ void fast_p3(RF_FAST_ARGS, int nk) {
   RF_FAST_BIND
   const int wGC = fc.wgc, wAU = fc.wau, wGU = fc.wgu;
-  const uint32_t *FA = F, *FG = F + 2 * MWS, *RC = R + MWS, *RU = R + 3 * MWS;
   for (int p = lane; p < nk; p += 32) {
     uint32_t key = 0;
     if (p < nlag) {
       const int s = lv - 1 - p;
-      const int i0 = p < lv ? 0 : p - lv + 1, i1 = p < lv ? p : lv - 1;
+      const int i0 = p < lv ? 0 : p - lv + 1;
+      const int d = p < lv ? p + 1 : 2 * lv - 1 - p;
+      const int iend = i0 + ((d + 1) >> 1); /* exclusive */
       int acc = 0;
-      for (int wi = i0 >> 5; wi <= (i1 >> 5); wi++) {
-        const unsigned fg = FG[wi], fa = FA[wi];
-        const unsigned rc = fast_shift(RC, wi, s), ru = fast_shift(RU, wi, s);
-        acc += wGC * __popc(fg & rc) + wAU * __popc(fa & ru) + wGU * __popc(fg & ru);
+      for (int wi = i0 >> 5; wi <= ((iend - 1) >> 5); wi++) {
+        const unsigned fh = FH[wi], fl = FL[wi];
+        const unsigned x = fh ^ fast_shift(RH, wi, s), y = fl ^ fast_shift(RL, wi, s);
+        unsigned range = FULL;
+        if (32 * wi < i0) range &= FULL << (i0 - 32 * wi);
+        if (32 * wi + 32 > iend) range &= FULL >> (32 * wi + 32 - iend);
+        const unsigned xy = x & y & range, t = fh ^ fl;
+        acc += wGC * __popc(xy & t) + wAU * __popc(xy & ~t) + wGU * __popc(~x & y & fh & range);
       }
-      const uint32_t norm = (uint32_t)(p < lv ? p : 2 * lv - 2 - p) + 1u;
-      key = ((((uint32_t)acc << RF_FAST_SHIFT) / norm) << RF_FAST_LAGBITS) | (uint32_t)p;
+      key = ((((uint32_t)acc << RF_FAST_SHIFT) / (uint32_t)d) << RF_FAST_LAGBITS) | (uint32_t)p;
     }
     keys[p] = key;
   }
@@ -345,10 +355,10 @@ __device__ __forceinline__ void fast_p4(RF_FAST_ARGS) {
   RF_FAST_BIND
   uint32_t vreg[K];
   fast_sort_regs<K>(keys, vreg, lane);
-  /* rank r = register r/32 of lane r%32 */
+  /* rank t = register t % K of lane t / K */
 #pragma unroll
   for (int q = 0; q < K; q++) {
-    const int r = 32 * q + lane;
+    const int r = K * lane + q;
     if (r < nr) rlag[r] = (uint16_t)(vreg[q] & ((1u << RF_FAST_LAGBITS) - 1));
   }
 }
@@ -366,38 +376,42 @@ __device__ __forceinline__ void fast_p5(RF_FAST_ARGS) {
     const int i0 = p < lv ? 0 : p - lv + 1;
     const int d = p < lv ? p + 1 : 2 * lv - 1 - p;
     const int len2 = (d + 1) >> 1;
-    const int iend = i0 + len2; /* exclusive */
-    int max_nb = 0, tmp_max = 0, max_i = 0, max_j = 0, last_i = -2;
+    int iend = i0 + len2; /* exclusive */
+    /* hairpin test (rafft.py:78): pos[j] - pos[i] decreases along the scan, so the positions
+     * that fail it are the innermost ones; they can never become the stem and are clipped */
+    while (iend > i0 && !((int)pos[p - (iend - 1)] - (int)pos[iend - 1] > prm.min_hp)) iend--;
+    int max_nb = 0, tmp_max = 0, max_i = 0, max_j = 0;
     double max_score = 0.0, prev = 0.0;
-    for (int wi = i0 >> 5; wi <= ((iend - 1) >> 5); wi++) {
-      const unsigned fa = F[wi], fcc = F[MWS + wi], fg = F[2 * MWS + wi], fu = F[3 * MWS + wi];
-      const unsigned ra = fast_shift(R, wi, s), rc = fast_shift(R + MWS, wi, s),
-                     rg = fast_shift(R + 2 * MWS, wi, s), ru = fast_shift(R + 3 * MWS, wi, s);
-      const unsigned gc = ((fg & rc) | (fcc & rg)) & mGC, au = ((fa & ru) | (fu & ra)) & mAU,
-                     gu = ((fg & ru) | (fu & rg)) & mGU;
+    unsigned carry = 0; /* was the position just before this word pairable (and in range)? */
+    unsigned best_bit = 0;
+    int best_wi = 0;
+    for (int wi = i0 >> 5; wi <= ((iend - 1) >> 5) && iend > i0; wi++) {
+      const unsigned fh = FH[wi], fl = FL[wi];
+      const unsigned x = fh ^ fast_shift(RH, wi, s), y = fl ^ fast_shift(RL, wi, s);
       unsigned range = FULL;
       if (32 * wi < i0) range &= FULL << (i0 - 32 * wi);
       if (32 * wi + 32 > iend) range &= FULL >> (32 * wi + 32 - iend);
-      unsigned Pm = (gc | au | gu) & range;
+      const unsigned xy = x & y & range, t = fh ^ fl;
+      const unsigned gc = xy & t & mGC, au = xy & ~t & mAU, gu = ~x & y & fh & range & mGU;
+      unsigned Pm = gc | au | gu;
+      const unsigned ADJ = (Pm << 1) | carry; /* the previous position is pairable too */
+      carry = Pm >> 31;
       /* both arms continue in original coordinates (rafft.py:67), t > 0 */
       unsigned IS = CL[wi] & fast_shift(CLR, wi, s - 1);
       if ((i0 >> 5) == wi) IS &= ~(1u << (i0 & 31));
       while (Pm) {
-        const int b = __ffs((int)Pm) - 1;
-        Pm &= Pm - 1;
-        const int i = 32 * wi + b;
-        const double w = ((gc >> b) & 1) ? dGC : ((au >> b) & 1) ? dAU : dGU;
-        const bool adjacent = last_i == i - 1;
+        const unsigned bit = Pm & (0u - Pm);
+        Pm ^= bit;
+        const double w = (gc & bit) ? dGC : (au & bit) ? dAU : dGU;
+        const bool adjacent = (ADJ & bit) != 0;
         double tot = w;
-        if ((IS >> b) & 1) tot = __dmul_rn(__dadd_rn(adjacent ? prev : 0.0, w), w);
+        if (IS & bit) tot = __dmul_rn(__dadd_rn(adjacent ? prev : 0.0, w), w);
         tmp_max = adjacent ? tmp_max + 1 : 1;
-        if (tot >= max_score && (int)pos[p - i] - (int)pos[i] > prm.min_hp) {
-          max_score = tot; max_nb = tmp_max; max_i = i; max_j = p - i;
-        }
+        if (tot >= max_score) { max_score = tot; max_nb = tmp_max; best_bit = bit; best_wi = wi; }
         prev = tot;
-        last_i = i;
       }
     }
+    if (best_bit) { max_i = 32 * best_wi + __ffs((int)best_bit) - 1; max_j = p - max_i; }
     w_scan += len2;
     r_stem[r] = ((uint32_t)max_i << 16) | (uint32_t)max_j;
     r_nb[r] = (uint16_t)max_nb;

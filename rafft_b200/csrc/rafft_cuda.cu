@@ -189,19 +189,25 @@ __device__ __forceinline__ void fast_class(const WaveCtx &c, int cls, char *ws, 
     char *arena = c.arenas + (size_t)j * (size_t)c.caps.arena_bytes;
     SeqState *st = c.states + j;
 #define RF_FAST_CALL c.E, c.prm, c.caps, c.fast, arena, c.aoff, st, v, ws, lane
-    if (has) fast_p1(RF_FAST_CALL);
-    __syncthreads();
-    if (has) fast_p2(RF_FAST_CALL);
-    __syncthreads();
-    if (has) fast_p3(RF_FAST_CALL, 32 * K);
-    __syncthreads();
-    if (has) fast_p4<K>(RF_FAST_CALL);
+    /* three code phases per region (set up + rank | scan | energies + records), separated by
+     * block barriers; warp barriers order the shared-memory traffic inside a phase */
+    if (has) {
+      fast_p1(RF_FAST_CALL);
+      __syncwarp();
+      fast_p2(RF_FAST_CALL);
+      __syncwarp();
+      fast_p3(RF_FAST_CALL, 32 * K);
+      __syncwarp();
+      fast_p4<K>(RF_FAST_CALL);
+    }
     __syncthreads();
     if (has) fast_p5(RF_FAST_CALL);
     __syncthreads();
-    if (has) fast_p6(RF_FAST_CALL);
-    __syncthreads();
-    if (has) fast_p7(RF_FAST_CALL);
+    if (has) {
+      fast_p6(RF_FAST_CALL);
+      __syncwarp();
+      fast_p7(RF_FAST_CALL);
+    }
 #undef RF_FAST_CALL
   }
 }
