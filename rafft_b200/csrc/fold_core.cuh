@@ -448,8 +448,6 @@ struct Arena {
   int32_t *todo;       /* todo_cap * 3 */
   int32_t *todo_id;    /* todo_cap */
   int32_t *flag, *pref; /* sel_cap = max(chunk_cap, new_cap + max_stack) */
-  int32_t *ch_e;       /* chunk_cap */
-  uint64_t *ch_lo, *ch_hi; /* chunk_cap */
 };
 
 /* Scratch of one node expansion (views into the warp's slice of Arena::wscratch). */
@@ -538,7 +536,7 @@ RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &
   RF_CARVE(pool16, int16_t, c.pool16_cap);
   RF_CARVE(cand, Cand, c.cand_cap);
   RF_CARVE(store, StoreRec, c.store_cap);
-  RF_CARVE(store_db, char, (size_t)c.store_cap * L);
+  RF_CARVE(store_db, char, (size_t)c.store_cap * (size_t)((L + 15) & ~15)); /* rows padded to 16 bytes */
   RF_CARVE(nlist, int32_t, c.nlist_cap);
   RF_CARVE(ncnt, int32_t, c.nlist_cap);
   RF_CARVE(seen_used, int32_t, c.seen_cap);
@@ -553,15 +551,12 @@ RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &
   RF_CARVE(todo_id, int32_t, c.todo_cap);
   RF_CARVE(flag, int32_t, sel_cap);
   RF_CARVE(pref, int32_t, sel_cap);
-  RF_CARVE(ch_e, int32_t, c.chunk_cap);
-  RF_CARVE(ch_lo, uint64_t, c.chunk_cap);
-  RF_CARVE(ch_hi, uint64_t, c.chunk_cap);
 #undef RF_CARVE
   return align_up(off, 256);
 }
 /* Byte offsets of the arena pieces (computed once on the host, bound per block/warp). */
 struct ArenaOff {
-  uint32_t seen, nht, code, node, pool16, cand, store, store_db, nlist, ncnt, seen_used, fresh, sel, sel_idx, sel_store, beam, traj_n, traj, todo, todo_id, flag, pref, ch_e, ch_lo, ch_hi;
+  uint32_t seen, nht, code, node, pool16, cand, store, store_db, nlist, ncnt, seen_used, fresh, sel, sel_idx, sel_store, beam, traj_n, traj, todo, todo_id, flag, pref;
 };
 RF_HD void arena_bind(Arena &A, char *base, const ArenaOff &o) {
   A.seen = (SeenEnt *)(base + o.seen);
@@ -586,9 +581,6 @@ RF_HD void arena_bind(Arena &A, char *base, const ArenaOff &o) {
   A.todo_id = (int32_t *)(base + o.todo_id);
   A.flag = (int32_t *)(base + o.flag);
   A.pref = (int32_t *)(base + o.pref);
-  A.ch_e = (int32_t *)(base + o.ch_e);
-  A.ch_lo = (uint64_t *)(base + o.ch_lo);
-  A.ch_hi = (uint64_t *)(base + o.ch_hi);
 }
 #ifndef __CUDACC_RTC__
 inline void arena_offsets(ArenaOff &o, const Caps &c, const FoldParams &fp) {
@@ -617,14 +609,49 @@ inline void arena_offsets(ArenaOff &o, const Caps &c, const FoldParams &fp) {
   o.todo_id = (uint32_t)((char *)A.todo_id - base);
   o.flag = (uint32_t)((char *)A.flag - base);
   o.pref = (uint32_t)((char *)A.pref - base);
-  o.ch_e = (uint32_t)((char *)A.ch_e - base);
-  o.ch_lo = (uint32_t)((char *)A.ch_lo - base);
-  o.ch_hi = (uint32_t)((char *)A.ch_hi - base);
 }
 #endif
 /* bytes at the start of an arena that hold the hash tables (zeroed by the host once) */
 RF_HD size_t arena_table_bytes(const Caps &c) {
   return align_up(sizeof(SeenEnt) * (size_t)c.seen_cap, 16) + sizeof(unsigned long long) * (size_t)c.nht_cap;
+}
+
+/* Block-shared working set of the combine phase (shared memory on the device): the chunk of
+ * stem combinations under examination, the list of beam members still to enumerate with the
+ * running sum of their product sizes, and a small hash table that finds duplicates INSIDE a chunk
+ * (children of different members can be the same structure; the first one in order wins). */
+struct CombineStage {
+  uint64_t *lo, *hi;          /* chunk_cap: fingerprints */
+  uint64_t *mb_pre;           /* max_stack + 1: first flattened index of the m-th open member */
+  uint64_t *mprod, *dprod;    /* max_stack: product of an open member / of an exhausted one */
+  int32_t *flag, *pref, *e;   /* chunk_cap */
+  int32_t *mem;               /* chunk_cap: open-member number of the item */
+  int32_t *mb_idx;            /* max_stack: beam slot of the m-th open member */
+  int32_t *htab;              /* hcap: item index + 1, 0 = empty */
+  int32_t hcap;               /* power of two >= 2 * chunk_cap */
+};
+RF_HD size_t stage_carve(CombineStage &S, char *base, int chunk_cap, int max_stack) {
+  size_t off = 0;
+  int hcap = 64;
+  while (hcap < 2 * chunk_cap) hcap <<= 1;
+  S.hcap = hcap;
+#define RF_SCARVE(field, type, count)              \
+  off = align_up(off, 16);                         \
+  S.field = (type *)(base ? base + off : nullptr); \
+  off += sizeof(type) * (size_t)(count);
+  RF_SCARVE(lo, uint64_t, chunk_cap);
+  RF_SCARVE(hi, uint64_t, chunk_cap);
+  RF_SCARVE(mb_pre, uint64_t, max_stack + 1);
+  RF_SCARVE(mprod, uint64_t, max_stack);
+  RF_SCARVE(dprod, uint64_t, max_stack);
+  RF_SCARVE(flag, int32_t, chunk_cap);
+  RF_SCARVE(pref, int32_t, chunk_cap);
+  RF_SCARVE(e, int32_t, chunk_cap);
+  RF_SCARVE(mem, int32_t, chunk_cap);
+  RF_SCARVE(mb_idx, int32_t, max_stack);
+  RF_SCARVE(htab, int32_t, hcap);
+#undef RF_SCARVE
+  return align_up(off, 16);
 }
 
 /* ------------------------------------------------------------------------------------ */
@@ -636,6 +663,7 @@ struct Fold {
   SeqState *sh;
   EnergyView ev;
   TaskQueue Q;
+  CombineStage cs; /* bound by the combine kernel only */
   RF_HD Fold(const DevEnergy *E_, const FoldParams &p, const Caps &c) : E(E_), prm(p), caps(c) {}
 
   /* --- node geometry ------------------------------------------------------------------ */
@@ -680,6 +708,11 @@ struct Fold {
     }
     return lo;
   }
+
+  /* dot-bracket rows of the structure store are padded to 16 bytes so that they move as vectors */
+  struct alignas(16) Vec16 { uint64_t a, b; };
+  RF_FN int db_stride() const { return (sh->L + 15) & ~15; }
+  RF_FN char *db_row(int store_idx) const { return A.store_db + (size_t)store_idx * (size_t)db_stride(); }
 
   RF_FN void fail(int code) {
     /* called by any thread: status only ever goes 0 -> code */
@@ -1034,6 +1067,35 @@ struct Fold {
     if (lo == 0) lo = 1; /* 0 marks an empty slot of the seen table */
   }
 
+  /* in-chunk duplicate detection: item i (fingerprint cs.lo/hi[i]) enters the table; items with
+   * the same fingerprint share a slot, which ends up holding the smallest item index + 1 */
+  RF_FN int chunk_insert(int i) {
+    const uint64_t lo = cs.lo[i], hi = cs.hi[i];
+    const unsigned mask = (unsigned)cs.hcap - 1;
+    unsigned slot = (unsigned)(lo ^ (hi >> 11) ^ (lo >> 29)) & mask;
+    for (;;) {
+      int v = cs.htab[slot];
+      if (v == 0) {
+        v = Exec::atomic_cas(&cs.htab[slot], 0, i + 1);
+        if (v == 0) return (int)slot;
+      }
+      if (cs.lo[v - 1] == lo && cs.hi[v - 1] == hi) {
+        Exec::atomic_min(&cs.htab[slot], i + 1);
+        return (int)slot;
+      }
+      slot = (slot + 1) & mask;
+    }
+  }
+  /* open member holding flattened combination index gi: last m with mb_pre[m] <= gi */
+  RF_FN int member_of(uint64_t gi, int nm) const {
+    int lo = 0, hi = nm - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (cs.mb_pre[mid] <= gi) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+  }
+
   /* ------------------------------------------------------------------------------------ */
   /* ---- phase: start of a fold ---------------------------------------------------------- */
   RF_FN void phase_init(const char *seq, int L, int seq_index) {
@@ -1174,117 +1236,151 @@ struct Fold {
         S.prod = mact ? prod : 0;
         if (mact == 0) S.done = 1;
       }
+      cs.mprod[b] = S.done ? 0 : S.prod;
+      cs.dprod[b] = S.done ? S.prod : 0;
     RF_PAR_END
+    /* the members still to enumerate ("open"), in beam order, and the running sum of their
+     * product sizes: the enumeration below runs over this flattened index space */
+    const uint64_t SAT = 1ULL << 62;
     RF_SINGLE_BEGIN
       sh->n_new = 0; sh->nb_branch = 0; sh->cur_b = 0;
+      int nm = 0;
+      uint64_t pre = 0;
+      for (int b = 0; b < beam_n; b++) {
+        if (cs.mprod[b]) {
+          cs.mb_idx[nm] = b; cs.mb_pre[nm] = pre; nm++;
+          pre = pre + cs.mprod[b] > SAT ? SAT : pre + cs.mprod[b];
+        }
+      }
+      cs.mb_pre[nm] = pre;
+      sh->tmp0 = nm;
     RF_SINGLE_END
-    /* P2b: members are enumerated one after the other while nb_branch < max_branch */
+    /* P2b: the open members are enumerated one after the other while nb_branch < max_branch
+     *      (rafft.py:180-203), a chunk of the flattened (member, combination) space at a time */
     const int CH = caps.chunk_cap;
-    for (;;) {
-      RF_SINGLE_BEGIN
-        int b = sh->cur_b;
-        while (b < beam_n && sh->nb_branch < prm.max_branch) {
-          const StoreRec &S = A.store[A.beam[b]];
-          if (!S.done) break;
-          /* a member whose product was exhausted earlier: the reference walks it again
-           * (every child is already in `seen`), we only account for it */
-          sh->cnt[CNT_COMBOS] += S.prod; sh->cnt[CNT_N_EVAL] += S.prod;
-          b++;
-        }
-        sh->cur_b = b;
-      RF_SINGLE_END
-      const int b = sh->cur_b;
-      if (b >= beam_n || sh->nb_branch >= prm.max_branch || sh->status != ST_OK) break;
-      StoreRec &S = A.store[A.beam[b]];
-      const uint64_t limit = S.prod;
-      uint64_t processed = 0;
-      bool cut = false;
-      while (processed < limit && !cut && sh->status == ST_OK) {
-        const int chunk = (int)((limit - processed) < (uint64_t)CH ? (limit - processed) : (uint64_t)CH);
-        /* evaluate + look up (rafft.py:192-196); children of one structure are distinct */
-        RF_PAR_BEGIN(i, chunk)
-          int e_; uint64_t lo_, hi_;
-          combo_eval(S, processed + (uint64_t)i, e_, lo_, hi_);
-          A.ch_e[i] = e_; A.ch_lo[i] = lo_; A.ch_hi[i] = hi_;
-          A.flag[i] = !seen_has(lo_, hi_);
-        RF_PAR_END
-        const int nnew = Exec::scan_flags(A.flag, A.pref, chunk, sh->wsum);
-        /* the reference breaks right after the combination that brings nb_branch to
-         * max_branch: unseen children number nb0 .. of this chunk are kept up to that one */
-        const int nb0 = sh->nb_branch, base = sh->n_new;
-        const int room = prm.max_branch - nb0; /* > 0 */
-        const int take = nnew < room ? nnew : room;
-        if (base + take > caps.new_cap || 2 * (sh->n_seen + take) + 2 > caps.seen_cap) {
-          RF_SINGLE_BEGIN fail(ST_ERR_CAPACITY); RF_SINGLE_END
-          break;
-        }
-        RF_SINGLE_BEGIN
-          sh->xcut = -1;
-        RF_SINGLE_END
-        RF_PAR_BEGIN(i, chunk)
-          if (A.flag[i] && A.pref[i] < take) {
-            NewRec &r = A.fresh[base + A.pref[i]];
-            r.e = A.ch_e[i]; r.parent_slot = b; r.combo = processed + (uint64_t)i;
-            r.fp_lo = A.ch_lo[i]; r.fp_hi = A.ch_hi[i];
-            seen_put(A.ch_lo[i], A.ch_hi[i]);
-            if (nnew >= room && A.pref[i] == take - 1) sh->xcut = i;
-          }
-        RF_PAR_END
-        const int xcut = sh->xcut;
-        const int upto = xcut >= 0 ? xcut + 1 : chunk;
-        RF_SINGLE_BEGIN
-          sh->n_new += take;
-          sh->nb_branch += take;
-          sh->cnt[CNT_COMBOS] += upto;
-          sh->cnt[CNT_N_EVAL] += upto;
-        RF_SINGLE_END
-        processed += (uint64_t)upto;
-        cut = xcut >= 0;
+    const int nm = sh->tmp0;
+    const uint64_t total = cs.mb_pre[nm];
+    uint64_t g = 0;
+    bool cut = false;
+    while (prm.max_branch > 0 && g < total && !cut && sh->status == ST_OK) {
+      const int chunk = (int)((total - g) < (uint64_t)CH ? (total - g) : (uint64_t)CH);
+      /* evaluate + look up in `seen` (rafft.py:192-196) */
+      RF_PAR_BEGIN(x, cs.hcap)
+        cs.htab[x] = 0;
+      RF_PAR_END
+      RF_PAR_BEGIN(i, chunk)
+        const uint64_t gi = g + (uint64_t)i;
+        const int m = member_of(gi, nm);
+        const StoreRec &S = A.store[A.beam[cs.mb_idx[m]]];
+        int e_; uint64_t lo_, hi_;
+        combo_eval(S, gi - cs.mb_pre[m], e_, lo_, hi_);
+        cs.e[i] = e_; cs.lo[i] = lo_; cs.hi[i] = hi_; cs.mem[i] = m;
+        cs.flag[i] = !seen_has(lo_, hi_);
+      RF_PAR_END
+      /* the same child reached from two members of this chunk: only the first one is new */
+      RF_PAR_BEGIN(i, chunk)
+        if (cs.flag[i]) cs.pref[i] = chunk_insert(i);
+      RF_PAR_END
+      RF_PAR_BEGIN(i, chunk)
+        if (cs.flag[i]) cs.flag[i] = cs.htab[cs.pref[i]] == i + 1;
+      RF_PAR_END
+      const int nnew = Exec::scan_flags(cs.flag, cs.pref, chunk, sh->wsum);
+      /* the reference breaks right after the combination that brings nb_branch to
+       * max_branch: unseen children number nb0 .. of this chunk are kept up to that one */
+      const int nb0 = sh->nb_branch, base = sh->n_new;
+      const int room = prm.max_branch - nb0; /* > 0 */
+      const int take = nnew < room ? nnew : room;
+      if (base + take > caps.new_cap || 2 * (sh->n_seen + take) + 2 > caps.seen_cap) {
+        RF_SINGLE_BEGIN fail(ST_ERR_CAPACITY); RF_SINGLE_END
+        break;
       }
       RF_SINGLE_BEGIN
-        if (processed == S.prod) S.done = 1;
-        sh->cur_b = b + 1;
+        sh->xcut = -1;
       RF_SINGLE_END
+      RF_PAR_BEGIN(i, chunk)
+        if (cs.flag[i] && cs.pref[i] < take) {
+          const int m = cs.mem[i];
+          NewRec &r = A.fresh[base + cs.pref[i]];
+          r.e = cs.e[i]; r.parent_slot = cs.mb_idx[m]; r.combo = g + (uint64_t)i - cs.mb_pre[m];
+          r.fp_lo = cs.lo[i]; r.fp_hi = cs.hi[i];
+          seen_put(cs.lo[i], cs.hi[i]);
+          if (nnew >= room && cs.pref[i] == take - 1) sh->xcut = i;
+        }
+      RF_PAR_END
+      const int xcut = sh->xcut;
+      const int upto = xcut >= 0 ? xcut + 1 : chunk;
+      RF_SINGLE_BEGIN
+        sh->n_new += take;
+        sh->nb_branch += take;
+      RF_SINGLE_END
+      g += (uint64_t)upto;
+      cut = xcut >= 0;
     }
     if (sh->status != ST_OK) { finish_fold(); return; }
+    /* which members were exhausted, where the enumeration stopped, and the reference's counters:
+     * an exhausted member met before the stop is walked again in full by the reference (all its
+     * children are in `seen`) */
+    RF_SINGLE_BEGIN
+      if (prm.max_branch > 0) {
+        int mc = nm;       /* open member the `break` happened in */
+        uint64_t lp = 0;   /* combinations of it that were examined */
+        if (cut) { mc = member_of(g - 1, nm); lp = g - cs.mb_pre[mc]; }
+        for (int m = 0; m < mc; m++) A.store[A.beam[cs.mb_idx[m]]].done = 1;
+        if (cut && lp == cs.mprod[cs.mb_idx[mc]]) A.store[A.beam[cs.mb_idx[mc]]].done = 1;
+        const int bcut = cut ? cs.mb_idx[mc] : beam_n;
+        uint64_t walked = g;
+        for (int b = 0; b < bcut; b++) walked += cs.dprod[b];
+        sh->cnt[CNT_COMBOS] += walked; sh->cnt[CNT_N_EVAL] += walked;
+        sh->cur_b = cut ? bcut + 1 : beam_n;
+      }
+    RF_SINGLE_END
     /* P2c: once nb_branch >= max_branch the `break` only leaves the product loop
      *      (rafft.py:202-203): every later member still tries its first combination */
     {
       const int b0 = sh->cur_b;
       const int rest = beam_n - b0;
       if (rest > 0) {
+        RF_PAR_BEGIN(x, cs.hcap)
+          cs.htab[x] = 0;
+        RF_PAR_END
         RF_PAR_BEGIN(j, rest)
-          const StoreRec &S = A.store[A.beam[b0 + j]];
-          A.flag[j] = 0;
-          if (!S.done) {
+          cs.flag[j] = 0;
+          if (cs.mprod[b0 + j]) {
+            const StoreRec &S = A.store[A.beam[b0 + j]];
             int e_; uint64_t lo_, hi_;
             combo_eval(S, 0, e_, lo_, hi_);
-            A.ch_e[j] = e_; A.ch_lo[j] = lo_; A.ch_hi[j] = hi_;
-            A.flag[j] = !seen_has(lo_, hi_);
+            cs.e[j] = e_; cs.lo[j] = lo_; cs.hi[j] = hi_;
+            cs.flag[j] = !seen_has(lo_, hi_);
           }
         RF_PAR_END
-        RF_SINGLE_BEGIN
-          for (int j = 0; j < rest; j++) {
-            StoreRec &S = A.store[A.beam[b0 + j]];
-            if (S.done) {
-              if (S.prod) { sh->cnt[CNT_COMBOS] += 1; sh->cnt[CNT_N_EVAL] += 1; }
-              continue;
+        RF_PAR_BEGIN(j, rest)
+          if (cs.flag[j]) cs.pref[j] = chunk_insert(j);
+        RF_PAR_END
+        RF_PAR_BEGIN(j, rest)
+          if (cs.flag[j]) cs.flag[j] = cs.htab[cs.pref[j]] == j + 1;
+        RF_PAR_END
+        const int nnew = Exec::scan_flags(cs.flag, cs.pref, rest, sh->wsum);
+        const int base = sh->n_new;
+        if (base + nnew > caps.new_cap || 2 * (sh->n_seen + nnew) + 2 > caps.seen_cap) {
+          RF_SINGLE_BEGIN fail(ST_ERR_CAPACITY); RF_SINGLE_END
+        } else {
+          RF_PAR_BEGIN(j, rest)
+            if (cs.flag[j]) {
+              NewRec &r = A.fresh[base + cs.pref[j]];
+              r.e = cs.e[j]; r.parent_slot = b0 + j; r.combo = 0;
+              r.fp_lo = cs.lo[j]; r.fp_hi = cs.hi[j];
+              seen_put(cs.lo[j], cs.hi[j]);
             }
-            sh->cnt[CNT_COMBOS] += 1; sh->cnt[CNT_N_EVAL] += 1;
-            if (A.flag[j] && !seen_has(A.ch_lo[j], A.ch_hi[j])) {
-              if (sh->n_new + 1 > caps.new_cap || 2 * (sh->n_seen + 1) + 2 > caps.seen_cap) {
-                fail(ST_ERR_CAPACITY);
-                break;
-              }
-              NewRec &r = A.fresh[sh->n_new++];
-              r.e = A.ch_e[j]; r.parent_slot = b0 + j; r.combo = 0;
-              r.fp_lo = A.ch_lo[j]; r.fp_hi = A.ch_hi[j];
-              seen_put(A.ch_lo[j], A.ch_hi[j]);
-              sh->nb_branch++;
-            }
-            if (S.prod == 1) S.done = 1;
-          }
-        RF_SINGLE_END
+            if (cs.mprod[b0 + j] == 1) A.store[A.beam[b0 + j]].done = 1;
+          RF_PAR_END
+          RF_SINGLE_BEGIN
+            int tried = 0;
+            for (int j = 0; j < rest; j++) tried += (cs.mprod[b0 + j] | cs.dprod[b0 + j]) != 0;
+            sh->cnt[CNT_COMBOS] += tried; sh->cnt[CNT_N_EVAL] += tried;
+            sh->n_new += nnew;
+            sh->nb_branch += nnew;
+          RF_SINGLE_END
+        }
       }
     }
     if (sh->status != ST_OK) finish_fold();
@@ -1478,15 +1574,20 @@ struct Fold {
       else { sh->n_nlist = nl; sh->n_store = at; }
     RF_SINGLE_END
     if (sh->status != ST_OK) { finish_fold(); return; }
-    /* copy the parent's dot-bracket */
-    RF_PAR_BEGIN(x, keep * L)
-      int r = x / L, pos = x - r * L;
-      int i = A.sel[r];
-      if (i < n_new) {
-        int parent = A.beam[A.fresh[i].parent_slot];
-        A.store_db[(size_t)A.sel_store[r] * L + pos] = A.store_db[(size_t)parent * L + pos];
+    /* copy the parent's dot-bracket: one warp per row, 16 bytes per lane */
+    Exec::sync();
+    {
+      const int nvec = db_stride() >> 4;
+      for (int r = Exec::warp(); r < keep; r += Exec::nwarps()) {
+        const int i = A.sel[r];
+        if (i < n_new) {
+          const Vec16 *src = (const Vec16 *)db_row(A.beam[A.fresh[i].parent_slot]);
+          Vec16 *dst = (Vec16 *)db_row(A.sel_store[r]);
+          for (int w = Exec::lane(); w < nvec; w += Exec::lanes()) dst[w] = src[w];
+        }
       }
-    RF_PAR_END
+    }
+    Exec::sync();
     /* stems + node list */
     RF_PAR_BEGIN(r, keep)
       int i = A.sel[r];
@@ -1494,7 +1595,7 @@ struct Fold {
         const NewRec &nr = A.fresh[i];
         const StoreRec &S = A.store[A.beam[nr.parent_slot]];
         StoreRec &C = A.store[A.sel_store[r]];
-        char *db = A.store_db + (size_t)A.sel_store[r] * L;
+        char *db = db_row(A.sel_store[r]);
         uint64_t combo = nr.combo;
         int w = C.nl_off + C.nl_n; /* filled backwards: nodes are visited last first */
         for (int k = S.nl_n - 1; k >= 0; k--) {
@@ -1563,9 +1664,13 @@ struct Fold {
       RF_PAR_BEGIN(k, nstruct)
         out.energy[s0 + k] = A.store[k].e;
       RF_PAR_END
-      RF_PAR_BEGIN(x, nstruct * L)
-        out.db[d0 + x] = A.store_db[x];
-      RF_PAR_END
+      Exec::sync();
+      for (int k = Exec::warp(); k < nstruct; k += Exec::nwarps()) {
+        const char *src = db_row(k);
+        char *dst = out.db + d0 + (int64_t)k * L;
+        for (int b = Exec::lane(); b < L; b += Exec::lanes()) dst[b] = src[b];
+      }
+      Exec::sync();
       RF_SINGLE_BEGIN
         int64_t e = e0;
         for (int s = 0; s < sh->n_steps; s++) {
@@ -1578,10 +1683,13 @@ struct Fold {
         out.energy[s0 + k] = A.store[A.beam[k]].e;
         out.entries[e0 + k] = k;
       RF_PAR_END
-      RF_PAR_BEGIN(x, nstruct * L)
-        int k = x / L;
-        out.db[d0 + x] = A.store_db[(size_t)A.beam[k] * L + (x - k * L)];
-      RF_PAR_END
+      Exec::sync();
+      for (int k = Exec::warp(); k < nstruct; k += Exec::nwarps()) {
+        const char *src = db_row(A.beam[k]);
+        char *dst = out.db + d0 + (int64_t)k * L;
+        for (int b = Exec::lane(); b < L; b += Exec::lanes()) dst[b] = src[b];
+      }
+      Exec::sync();
       RF_SINGLE_BEGIN
         out.step_n[t0] = nstruct;
       RF_SINGLE_END

@@ -116,7 +116,9 @@ __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_gather(RF_WAVE_PARAM) 
 __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_combine(RF_WAVE_PARAM) {
   __shared__ SeqState sh;
   Fold f(c.E, c.prm, c.caps);
+  extern __shared__ __align__(16) char combine_smem[];
   if (!BlockBind::load(c, f, &sh, true)) return;
+  stage_carve(f.cs, combine_smem, c.caps.chunk_cap, c.prm.max_stack);
   f.phase_combine();
   BlockBind::store(c, &sh);
 }
@@ -729,6 +731,9 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     const size_t fast_smem = (size_t)(fsh.threads / 32) * (size_t)fastcfg.smem_per_warp;
     const bool any_generic = fcap == 0 || Lr > fastcfg.L_cap || Lr / 2 > fastcfg.br_cap;
     wc.out = O;
+    CombineStage cs_probe;
+    const size_t stage_bytes = stage_carve(cs_probe, nullptr, caps.chunk_cap, F.max_stack);
+    CK(cudaFuncSetAttribute(k_combine, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stage_bytes));
     const int egrid = ctx->sm_count * ctx->blocks_per_sm;
     if (fcap > 0) CK(cudaFuncSetAttribute(fsh.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast_smem));
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
@@ -756,7 +761,7 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
           k_expand<5><<<egrid, 128, 0, ctx->stream>>>(wc);
           launches += 5;
         }
-        k_combine<<<nw, T, 0, ctx->stream>>>(wc);
+        k_combine<<<nw, T, stage_bytes, ctx->stream>>>(wc);
         k_select<<<nw, T, 0, ctx->stream>>>(wc);
         k_materialise<<<nw, T, 0, ctx->stream>>>(wc);
         launches += 3;

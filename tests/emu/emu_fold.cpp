@@ -52,6 +52,9 @@ int emu_fold(const rafft_energy_params *ep_in, const char *seq, int L, const raf
   std::vector<char> scratch((size_t)caps.wscratch_bytes);
   f.Q.n_tasks = &n_tasks; f.Q.cap = qcap; f.Q.task = tasks.data(); f.Q.scratch = scratch.data(); f.Q.self = 0;
   f.Q.n_fast = nullptr; f.Q.fast_cap = 0; f.Q.fast_lv = 0; f.Q.fast_br = 0; f.Q.fast_task = nullptr; /* CUDA-only path */
+  CombineStage probe;
+  std::vector<char> stage(stage_carve(probe, nullptr, caps.chunk_cap, F.max_stack) + 64);
+  stage_carve(f.cs, (char *)(((uintptr_t)stage.data() + 15) & ~(uintptr_t)15), caps.chunk_cap, F.max_stack);
   /* output for one sequence */
   int64_t scap = (int64_t)caps.store_cap, ecap = (int64_t)caps.step_cap * F.max_stack;
   std::vector<int32_t> status(1), nstruct(1), nstep(1), energy(scap), step_n(caps.step_cap), entries(ecap);
