@@ -39,6 +39,9 @@ WORKLOADS = {
     "cfg4": dict(gen="cfg4", count=1000, nb_mode=200, max_stack=200,
                  desc="1k synthetic 3,000-nt RNAs, -n 200 -ms 200"),
 }
+# dram__bytes_read.sum + dram__bytes_write.sum of k_expand_fast per launch (average over the launches
+# of one step) from the ncu --set full capture under profiles/ (null until one exists for the workload)
+TRAFFIC = {}
 METRIC = "sequences folded/sec"
 UNIT = "seq/s"
 
@@ -66,27 +69,39 @@ def peaks():
 
 def cpu_sample(seqs, want):
     "stratified subsample: every k-th sequence of the batch"
+    want = max(1, min(want, len(seqs)))
     k = max(1, len(seqs) // want)
     return seqs[::k][:want], k
 
 
-def algorithmic_bytes(counters, lengths):
+def cpu_sample_for(pyoracle, seqs, wl, cores, target_s):
+    """Stratified sample of the workload that keeps the CPU restatement busy for about target_s
+    seconds on `cores` threads (a 64-sequence pilot measures the rate first)."""
+    pilot, _ = cpu_sample(seqs, 64)
+    t0 = time.perf_counter()
+    pyoracle.fold_batch(pilot, wl["nb_mode"], wl["max_stack"], 1000, nthreads=cores, want_text=False)
+    rate = len(pilot) / max(time.perf_counter() - t0, 1e-3)
+    return cpu_sample(seqs, int(rate * target_s))
+
+
+def algorithmic_bytes(counters, lengths, which="n_eval"):
     """one int16 pair table read per evaluated structure, the position list of
-    every expanded region, and the emitted structures (reference granularity)."""
+    every expanded region (reference granularity).  which = "n_eval": the whole path;
+    "n_eval_expand": the share of the region expansion (find_best_consecutives, rafft.py:98)."""
     import numpy as np
     L = np.asarray(lengths, dtype=np.int64)
     c = counters
     from rafft_b200._native import COUNTER_NAMES as CN
-    n_eval, node_pos = c[:, CN.index("n_eval")], c[:, CN.index("node_pos")]
+    n_eval, node_pos = c[:, CN.index(which)], c[:, CN.index("node_pos")]
     return n_eval * 2 * (L + 1) + node_pos * 2
 
 
-def algorithmic_intops(counters, lengths):
+def algorithmic_intops(counters, lengths, which="n_eval"):
     import numpy as np
     from rafft_b200._native import COUNTER_NAMES as CN
     L = np.asarray(lengths, dtype=np.int64)
     c = counters
-    return c[:, CN.index("w_corr")] + c[:, CN.index("w_scan")] + c[:, CN.index("n_eval")] * (L + 1)
+    return c[:, CN.index("w_corr")] + c[:, CN.index("w_scan")] + c[:, CN.index(which)] * (L + 1)
 
 
 class ClockSampler:
@@ -151,9 +166,11 @@ def run_reference(args, wl):
     import pyoracle
     from rafft_b200.synth import config_batch
     seqs = config_batch(wl["gen"], (args.count or wl["count"]))
-    want = args.cpu_sample or {"cfg2": 512, "cfg3": 64, "cfg4": 2}[args.workload]
-    sample, k = cpu_sample(seqs, want)
     cores = os.cpu_count() or 1
+    if args.cpu_sample:
+        sample, k = cpu_sample(seqs, args.cpu_sample)
+    else:  # each timed step ~8 s of host work, so that K steps + warm-up end within minutes
+        sample, k = cpu_sample_for(pyoracle, seqs, wl, cores, 12.0)
     for _ in range(args.warmup):
         pyoracle.fold_batch(sample[:max(1, len(sample) // 8)], wl["nb_mode"], wl["max_stack"], 1000, nthreads=cores,
                             want_text=False)
@@ -223,7 +240,7 @@ def run_b200(args, wl):
         flush.zero_()
         torch.cuda.synchronize()
         return ctx.fold_raw_device(d_seqs.data_ptr(), d_offs.data_ptr(), n_local, int(offs[-1]),
-                                   int(lengths.max()), params, keep=False)
+                                   int(lengths.max()), params)
 
     def step_host():
         flush.zero_()
@@ -235,18 +252,20 @@ def run_b200(args, wl):
     for _ in range(args.warmup):
         raw = step_device()
     assert (raw.status == 0).all(), "a sequence failed: %s" % np.bincount(raw.status)
-    counters = raw.counters
+    counters = raw.counters.copy()  # views die with the result
 
     # ---- device-resident leg: CUDA events inside the library, on its launch stream
     sampler = ClockSampler(local)
     barrier()
     sampler.start()
     wall0 = time.perf_counter()
-    kernel_ms, launches = 0.0, 0
+    kernel_ms, launches, expand_ms, expand_launches = 0.0, 0, 0.0, 0
     for _ in range(args.steps):
         raw = step_device()
         kernel_ms += raw.kernel_ms
         launches += raw.kernel_launches
+        expand_ms += raw.expand_ms
+        expand_launches += raw.expand_launches
     barrier()
     wall_dev = time.perf_counter() - wall0
     clocks = sampler.stop()
@@ -270,12 +289,20 @@ def run_b200(args, wl):
     kernel_ms_max, e2e_max, wall_dev_max = [float(x) for x in t.cpu()]
     h2d_all, d2h_all, launches_all = [int(x) for x in tot.cpu()]
 
-    # roofline of the dominant kernel (fold_kernel; it is >99% of kernel_ms) on this rank
+    # roofline of the dominant kernel, k_expand_fast (region expansion; ~60% of the step): its
+    # algorithmic bytes/int-ops (the expansion share of the reference formulation)
+    # over its own launch durations, CUDA events around every launch inside the library
     peak, peak_src = peaks()
-    alg_bytes = int(algorithmic_bytes(counters, lengths).sum()) + int(raw.d2h_bytes)
-    alg_iops = int(algorithmic_intops(counters, lengths).sum())
-    per_launch_s = kernel_ms / args.steps / 1e3
-    achieved = alg_bytes / per_launch_s / 1e9
+    step_bytes = int(algorithmic_bytes(counters, lengths).sum()) + int(raw.d2h_bytes)
+    step_iops = int(algorithmic_intops(counters, lengths).sum())
+    exp_bytes = int(algorithmic_bytes(counters, lengths, "n_eval_expand").sum())
+    exp_iops = int(algorithmic_intops(counters, lengths, "n_eval_expand").sum())
+    n_exp = max(1, expand_launches)
+    exp_launch_s = max(expand_ms, 1e-6) / n_exp / 1e3          # average launch duration
+    exp_bytes_launch = exp_bytes * args.steps / n_exp           # algorithmic bytes per launch
+    exp_iops_launch = exp_iops * args.steps / n_exp
+    achieved = exp_bytes_launch / exp_launch_s / 1e9
+    per_step_s = kernel_ms / args.steps / 1e3
 
     line = None
     if rank == 0:
@@ -291,8 +318,7 @@ def run_b200(args, wl):
                        "parallelism": "sequences sharded over %d GPU(s), no collective" % world,
                        "shard_imbalance": imbalance([len(s) for s in seqs_all], shards, wl["max_stack"]),
                        "l2": "256 MiB flush buffer written between timed steps",
-                       "block_threads": int(os.environ.get("RAFFT_BLOCK_THREADS", "128")),
-                       "blocks_per_sm": int(os.environ.get("RAFFT_BLOCKS_PER_SM", "8"))},
+                       "waves": "all sequences resident (one arena each)"},
             "nt_per_s": total_nt * args.steps / (kernel_ms_max / 1e3),
             "wall_ms_per_step_device_inputs": wall_dev_max / args.steps * 1e3,
             "e2e": {"value": n_total * args.steps / e2e_max, "unit": UNIT,
@@ -301,19 +327,30 @@ def run_b200(args, wl):
             "gpu_launches": launches_all,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "kernel": "fold_kernel", "algorithmic_bytes_per_launch": alg_bytes,
-                         "alu": {"algorithmic_int_ops_per_launch": alg_iops,
-                                 "achieved_Giops": alg_iops / per_launch_s / 1e9,
+                         "frac": achieved / peak, "traffic": TRAFFIC.get(args.workload),
+                         "peak_source": peak_src, "kernel": "k_expand_fast",
+                         "launches_per_step": n_exp / args.steps,
+                         "avg_launch_ms": exp_launch_s * 1e3,
+                         "share_of_step": expand_ms / max(kernel_ms, 1e-9),
+                         "algorithmic_bytes_per_launch": exp_bytes_launch,
+                         "note": "algorithmic bytes = the reference formulation's traffic (one pair table per "
+                                 "evaluated stem + region position lists); the kernel is INT-issue bound, see alu",
+                         "alu": {"algorithmic_int_ops_per_launch": exp_iops_launch,
+                                 "achieved_Giops": exp_iops_launch / exp_launch_s / 1e9,
                                  "nominal_peak_Giops": 148 * 128 * 1.965,
-                                 "frac_of_nominal": alg_iops / per_launch_s / 1e9 / (148 * 128 * 1.965)}},
+                                 "frac_of_nominal": exp_iops_launch / exp_launch_s / 1e9 / (148 * 128 * 1.965)},
+                         "whole_step": {"algorithmic_bytes": step_bytes, "achieved": step_bytes / per_step_s / 1e9,
+                                        "frac": step_bytes / per_step_s / 1e9 / peak,
+                                        "algorithmic_int_ops": step_iops}},
         }
         if not args.no_cpu_baseline:
             sys.path.insert(0, os.path.join(ROOT, "oracle"))
             import pyoracle  # CPU baseline leg only
-            want = args.cpu_sample or {"cfg2": 512, "cfg3": 64, "cfg4": 2}[args.workload]
-            sample, k = cpu_sample(seqs_all, want)
             cores = os.cpu_count() or 1
+            if args.cpu_sample:
+                sample, k = cpu_sample(seqs_all, args.cpu_sample)
+            else:  # about 15 s of host work
+                sample, k = cpu_sample_for(pyoracle, seqs_all, wl, cores, 25.0)
             t0 = time.perf_counter()
             pyoracle.fold_batch(sample, wl["nb_mode"], wl["max_stack"], 1000, nthreads=cores, want_text=False)
             dt = time.perf_counter() - t0

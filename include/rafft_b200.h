@@ -76,6 +76,7 @@ enum {
   RAFFT_CNT_NODE_POS,     /* sum over the reference's create_childs calls of the region length Lv */
   RAFFT_CNT_T0_NS,        /* device globaltimer when the fold of this sequence started ... */
   RAFFT_CNT_T1_NS,        /* ... and ended (diagnostics: schedule / tail analysis) */
+  RAFFT_CNT_N_EVAL_EXPAND,/* the part of N_EVAL made by find_best_consecutives (rafft/rafft.py:98) */
   RAFFT_CNT_N
 };
 
@@ -101,6 +102,8 @@ typedef struct rafft_result {
   double kernel_ms;             /* device time of the fold kernel(s), CUDA events */
   int64_t kernel_launches;      /* number of kernel launches this call made */
   int64_t h2d_bytes, d2h_bytes; /* bytes copied host->device / device->host by this call */
+  double expand_ms;             /* device time of the region-expansion kernel launches alone */
+  int64_t expand_launches;      /* ... and how many of them there were */
 } rafft_result;
 
 typedef struct rafft_ctx rafft_ctx;

@@ -464,7 +464,7 @@ __device__ __forceinline__ void fast_p7(RF_FAST_ARGS) {
     fast_sort_dispatch(ck, nkc, lane);
     if (lane == 0) {
       off = atomicAdd(&st->n_cand, keep_n);
-      if (off + keep_n > caps.cand_cap) { st->status = ST_ERR_CAPACITY; off = -1; }
+      if (off + keep_n > caps.cand_cap) { st->status = ST_ERR_CAPACITY; st->fail_line = -__LINE__; off = -1; }
     }
     off = __shfl_sync(FULL, off, 0);
     if (off >= 0) {

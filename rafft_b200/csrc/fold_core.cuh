@@ -131,7 +131,8 @@ struct OutBuf {
 };
 
 enum { CNT_STEPS = 0, CNT_NODE_EXP, CNT_W_CORR, CNT_W_SCAN, CNT_N_EVAL, CNT_UNIQ_NODES,
-       CNT_UNIQ_W_CORR, CNT_UNIQ_W_SCAN, CNT_COMBOS, CNT_NODE_POS, CNT_T0_NS, CNT_T1_NS, CNT_N };
+       CNT_UNIQ_W_CORR, CNT_UNIQ_W_SCAN, CNT_COMBOS, CNT_NODE_POS, CNT_T0_NS, CNT_T1_NS, CNT_N_EVAL_EXPAND,
+       CNT_N };
 
 enum { ST_OK = 0, ST_ERR_SEQ = 2, ST_ERR_CAPACITY = 4 };
 
@@ -473,6 +474,7 @@ struct SeqState {
   int32_t n_node, n_pool16, n_cand, n_store, n_nlist, n_seen, n_todo, n_expand;
   int32_t beam_n, n_new, nb_branch, n_steps, n_traj;
   int32_t tmp0, tmp1, tmp2, cur_b, xcut;
+  int32_t fail_line, pad0_; /* source line of the first capacity failure (diagnostics) */
   int32_t emin, emax, cnt_le;
   int32_t wsum[12];
   int64_t seq_off;         /* first letter of the sequence in the batch text */
@@ -714,10 +716,12 @@ struct Fold {
   RF_FN int db_stride() const { return (sh->L + 15) & ~15; }
   RF_FN char *db_row(int store_idx) const { return A.store_db + (size_t)store_idx * (size_t)db_stride(); }
 
-  RF_FN void fail(int code) {
+  RF_FN void fail_at(int code, int line) {
     /* called by any thread: status only ever goes 0 -> code */
     sh->status = code;
+    sh->fail_line = line;
   }
+#define fail(code) fail_at(code, __LINE__)
   RF_FN void count(int which, long long v) {
     Exec::atomic_add64(&sh->cnt[which], (unsigned long long)v);
   }
@@ -1105,7 +1109,7 @@ struct Fold {
       sh->n_node = 0; sh->n_pool16 = 0; sh->n_cand = 0; sh->n_store = 0; sh->n_nlist = 0;
       sh->n_seen = 0; sh->n_todo = 0; sh->n_expand = 0; sh->beam_n = 0; sh->n_new = 0;
       sh->nb_branch = 0; sh->n_steps = 0; sh->n_traj = 0;
-      sh->active = 1; sh->stage = 0; sh->expand_pending = 0;
+      sh->active = 1; sh->stage = 0; sh->expand_pending = 0; sh->fail_line = 0;
       for (int k = 0; k < CNT_N; k++) sh->cnt[k] = 0;
       sh->cnt[CNT_T0_NS] = (unsigned long long)Exec::now_ns();
       if (L > caps.L_max) sh->status = ST_ERR_CAPACITY;
@@ -1230,7 +1234,7 @@ struct Fold {
         }
       }
       count(CNT_NODE_EXP, S.nl_n); count(CNT_NODE_POS, c_pos); count(CNT_W_CORR, c_corr);
-      count(CNT_W_SCAN, c_scan); count(CNT_N_EVAL, c_eval);
+      count(CNT_W_SCAN, c_scan); count(CNT_N_EVAL, c_eval); count(CNT_N_EVAL_EXPAND, c_eval);
       if (!S.done) {
         S.nact = mact;
         S.prod = mact ? prod : 0;
@@ -1654,6 +1658,7 @@ struct Fold {
       out.seq_step[si] = (int64_t)t0; out.seq_nstep[si] = nstep;
       out.seq_entry[si] = (int64_t)e0;
       for (int k = 0; k < CNT_N; k++) out.counters[(size_t)si * CNT_N + k] = (int64_t)sh->cnt[k];
+      if (sh->status != ST_OK) out.counters[(size_t)si * CNT_N + CNT_T1_NS] = sh->fail_line; /* diagnostics */
       sh->tmp0 = nstruct;
     RF_SINGLE_END
     const int nstruct = sh->tmp0;
@@ -1696,5 +1701,6 @@ struct Fold {
     }
   }
 };
+#undef fail
 
 }  // namespace rafft

@@ -149,10 +149,11 @@ inline Caps make_caps(int L_max, const FoldParams &F, int nthreads, int scale) {
   int64_t kmin = 2 * (int64_t)c.L_max > F.nb_mode ? 2 * (int64_t)c.L_max : F.nb_mode;
   c.key_cap = pow2_at_least(kmin < 32 ? 32 : kmin);
   c.mask_words = c.L_max / 32 + 2;
-  c.node_cap = (int32_t)((256 + 6 * ms + 2 * (int64_t)c.L_max) * scale);
+  const int64_t node_base = (256 + 6 * ms + 2 * (int64_t)c.L_max) * scale;
+  c.node_cap = (int32_t)(node_base * 3 / 2); /* loop records are small; the stems dominate */
   c.pool16_cap = c.node_cap * 12;
   int per_node = F.nb_mode / 4 < 8 ? 8 : F.nb_mode / 4 > 64 ? 64 : F.nb_mode / 4;
-  c.cand_cap = c.node_cap * per_node;
+  c.cand_cap = (int32_t)(node_base * per_node);
   c.store_cap = (int32_t)(1 + ms * 12 * scale);
   c.nlist_cap = c.store_cap * 12;
   c.new_cap = (int32_t)(mbc + ms + 1);

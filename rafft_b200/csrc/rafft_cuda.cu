@@ -16,6 +16,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <algorithm>
+#include <chrono>
 #include <string>
 #include <vector>
 #include "host_common.h"
@@ -392,7 +393,7 @@ struct rafft_ctx {
   int device = 0;
   int sm_count = 148;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, evx0 = nullptr, evx1 = nullptr;
   DevEnergy *d_energy = nullptr;
   DevBuf arenas, seqs, offs, order, subset, idx, big, ordered, scan, evalbuf, states, tasks, ftasks, scratch, small;
   std::vector<HostBlock> pinned_free;
@@ -428,6 +429,7 @@ static std::string g_create_err;
 
 static int dev_reserve(rafft_ctx *ctx, DevBuf &b, size_t bytes) {
   if (bytes <= b.cap) return RAFFT_OK;
+  if (getenv("RAFFT_DEBUG_ALLOC")) fprintf(stderr, "[rafft] cudaMalloc %zu bytes (had %zu)\n", bytes, b.cap);
   if (b.p) { CK(cudaFree(b.p)); b.p = nullptr; b.cap = 0; }
   size_t want = bytes + bytes / 8 + 256;
   cudaError_t e = cudaMalloc(&b.p, want);
@@ -459,6 +461,7 @@ static int host_block_get(rafft_ctx *ctx, size_t bytes, HostBlock *hb) {
   for (auto &b : ctx->pinned_free) cudaFreeHost(b.p);
   ctx->pinned_free.clear();
   size_t want = bytes + bytes / 4 + 4096;
+  if (getenv("RAFFT_DEBUG_ALLOC")) fprintf(stderr, "[rafft] cudaHostAlloc %zu bytes (request %zu)\n", want, bytes);
   CK(cudaHostAlloc(&hb->p, want, cudaHostAllocDefault));
   hb->cap = want;
   return RAFFT_OK;
@@ -487,6 +490,8 @@ void rafft_destroy(rafft_ctx *ctx) {
   if (ctx->d_energy) cudaFree(ctx->d_energy);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->evx0) cudaEventDestroy(ctx->evx0);
+  if (ctx->evx1) cudaEventDestroy(ctx->evx1);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -527,6 +532,8 @@ int rafft_create(rafft_ctx **out, int cuda_device, const rafft_energy_params *ep
     CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&ctx->ev0));
     CK(cudaEventCreate(&ctx->ev1));
+    CK(cudaEventCreate(&ctx->evx0));
+    CK(cudaEventCreate(&ctx->evx1));
     CK(cudaMalloc((void **)&ctx->d_energy, sizeof(DevEnergy)));
     CK(cudaMemcpy(ctx->d_energy, D, sizeof(DevEnergy), cudaMemcpyHostToDevice));
     CK(cudaHostAlloc((void **)&ctx->h_small, 64 * sizeof(int64_t), cudaHostAllocDefault));
@@ -594,6 +601,11 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
                        int32_t n, const rafft_params *params, rafft_result **out_res,
                        int64_t h2d_bytes) {
   std::string err;
+  const bool dbg = getenv("RAFFT_DEBUG_ALLOC") != nullptr;
+  auto t_start = std::chrono::steady_clock::now();
+  auto lap = [&](const char *what) {
+    if (dbg) fprintf(stderr, "[rafft] %-18s +%.2f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count());
+  };
   FoldParams F;
   if (!build_fold_params(params, &F, err)) { ctx->err = "rafft_fold_batch: " + err; return RAFFT_ERR_ARG; }
   int L_max = 1;
@@ -614,6 +626,8 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
   auto fail = [&](int rc) { rafft_result_free(&R->pub); return rc; };
   int64_t launches = 0, d2h = 0;
   float kernel_ms = 0.f;
+  double expand_ms = 0.0;
+  int64_t expand_launches = 0;
 
   /* index part of the output */
   OutBuf O;
@@ -750,7 +764,9 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
         k_gather<<<nw, T, 0, ctx->stream>>>(wc);
         launches++;
         if (fcap > 0) {
+          CK(cudaEventRecord(ctx->evx0, ctx->stream));
           fsh.fn<<<ctx->sm_count * fsh.blocks, fsh.threads, fast_smem, ctx->stream>>>(wc);
+          CK(cudaEventRecord(ctx->evx1, ctx->stream));
           launches++;
         }
         if (any_generic) {
@@ -768,6 +784,12 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
         CK(cudaMemcpyAsync(ctx->h_small + 16, (int32_t *)ctx->small.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
         CK(cudaStreamSynchronize(ctx->stream));
         d2h += 8;
+        if (fcap > 0) {
+          float xms = 0.f;
+          CK(cudaEventElapsedTime(&xms, ctx->evx0, ctx->evx1));
+          expand_ms += xms;
+          expand_launches++;
+        }
         const int32_t *hs = (const int32_t *)(ctx->h_small + 16);
         if (hs[1] == 0) break;
         if (it > 100000) { ctx->err = "rafft_fold_batch: no progress"; return fail(RAFFT_ERR_CUDA); }
@@ -788,10 +810,19 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     todo.clear();
     for (int i = 0; i < n; i++)
       if (h_status[i] == ST_ERR_CAPACITY) todo.push_back(i);
+    if (dbg && !todo.empty()) {
+      std::vector<int64_t> hc((size_t)n * CNT_N);
+      cudaMemcpy(hc.data(), O.counters, sizeof(int64_t) * hc.size(), cudaMemcpyDeviceToHost);
+      fprintf(stderr, "[rafft] round %d: %zu sequences over capacity (scale %d):", round, todo.size(), scale);
+      for (size_t k = 0; k < todo.size() && k < 12; k++)
+        fprintf(stderr, " #%d L=%lld line %lld;", todo[k], (long long)(h_offs[todo[k] + 1] - h_offs[todo[k]]), (long long)hc[(size_t)todo[k] * CNT_N + CNT_T1_NS]);
+      fprintf(stderr, "\n");
+    }
     if (todo.empty() || round >= 5) break;
     scale *= 4;
   }
 
+  lap("fold rounds done");
   /* ordered layout on the device, then one copy per array into pinned host memory */
   int64_t *d_scan = nullptr;
   size_t scan_bytes = sizeof(int64_t) * (4 * (size_t)(n + 1) + 8);
@@ -827,7 +858,9 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
   size_t h_status_o = o_end, h_soff = align_up(h_status_o + sizeof(int32_t) * (size_t)n, 16),
          h_doff = h_soff + sizeof(int64_t) * (size_t)(n + 1), h_toff = h_doff + sizeof(int64_t) * (size_t)(n + 1),
          h_cnt = h_toff + sizeof(int64_t) * (size_t)(n + 1), h_end = h_cnt + sizeof(int64_t) * (size_t)n * CNT_N;
+  lap("scan+pack queued");
   if (int rc = host_block_get(ctx, h_end + 64, &R->block)) return fail(rc);
+  lap("host block");
   char *hb = (char *)R->block.p;
   CK(cudaMemcpyAsync(hb, dord, o_end, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaMemcpyAsync(hb + h_soff, d_scan, sizeof(int64_t) * 3 * (size_t)(n + 1), cudaMemcpyDeviceToHost, ctx->stream));
@@ -837,6 +870,7 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
   float ms2 = 0.f;
   CK(cudaEventElapsedTime(&ms2, ctx->ev0, ctx->ev1));
   kernel_ms += ms2;
+  lap("d2h done");
   memcpy(hb + h_status_o, h_status.data(), sizeof(int32_t) * (size_t)n);
   rafft_result &P = R->pub;
   P.n_seq = n;
@@ -853,6 +887,8 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
   P.kernel_launches = launches;
   P.h2d_bytes = h2d_bytes;
   P.d2h_bytes = d2h;
+  P.expand_ms = expand_ms;
+  P.expand_launches = expand_launches;
   *out_res = &R->pub;
   return RAFFT_OK;
 }

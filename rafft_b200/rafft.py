@@ -4,6 +4,7 @@
 (correlation, lag ranking, stem scan, energy evaluation, beam search) runs on the GPU
 through the C-ABI in include/rafft_b200.h; this module only marshals arguments/results."""
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -43,7 +44,8 @@ class FoldContext:
     # -- raw calls ---------------------------------------------------------------------
     def fold_raw(self, seq_bytes, offs, params):
         """seq_bytes: concatenated ASCII letters; offs: int64 numpy array (n+1).
-        Returns a RawResult (numpy copies of the library-owned arrays)."""
+        Returns a RawResult: numpy VIEWS of the library-owned (pinned) arrays, valid until its
+        close() / garbage collection hands the memory back to the library."""
         offs = np.ascontiguousarray(offs, dtype=np.int64)
         n = len(offs) - 1
         res = C.POINTER(N.Result)()
@@ -51,22 +53,16 @@ class FoldContext:
                                         n, C.byref(params), C.byref(res))
         if rc != N.RAFFT_OK:
             raise self._err(rc)
-        try:
-            return RawResult(res.contents, offs)
-        finally:
-            self._lib.rafft_result_free(res)
+        return RawResult(res, offs, self._lib)
 
-    def fold_raw_device(self, d_seqs_ptr, d_offs_ptr, n, total_len, max_len, params, keep=True):
+    def fold_raw_device(self, d_seqs_ptr, d_offs_ptr, n, total_len, max_len, params):
         """Inputs already on this context's device (raw device pointers)."""
         res = C.POINTER(N.Result)()
         rc = self._lib.rafft_fold_batch_device(self._h, C.c_void_p(d_seqs_ptr), C.c_void_p(d_offs_ptr),
                                                n, total_len, max_len, C.byref(params), C.byref(res))
         if rc != N.RAFFT_OK:
             raise self._err(rc)
-        try:
-            return RawResult(res.contents, None, copy=keep)
-        finally:
-            self._lib.rafft_result_free(res)
+        return RawResult(res, None, self._lib)
 
     def eval_structures(self, seqs, structs):
         "integer energies (dcal/mol) of whole structures; replaces fold_compound.eval_structure"
@@ -93,32 +89,47 @@ def _np(ptr, count, dtype):
 
 
 class RawResult:
-    """Arrays of one rafft_result (see include/rafft_b200.h)."""
+    """Arrays of one rafft_result (see include/rafft_b200.h), as zero-copy views of the memory the
+    library owns; close() (or garbage collection) calls rafft_result_free."""
 
-    def __init__(self, r, offs, copy=True):
+    def __init__(self, res, offs, lib):
+        self._res, self._lib = res, lib
+        r = res.contents
         n = r.n_seq
         self.n_seq = n
         self.kernel_ms = r.kernel_ms
         self.kernel_launches = r.kernel_launches
+        self.expand_ms = r.expand_ms
+        self.expand_launches = r.expand_launches
         self.h2d_bytes, self.d2h_bytes = r.h2d_bytes, r.d2h_bytes
-        self.status = _np(r.status, n, np.int32).copy()
-        self.struct_off = _np(r.struct_off, n + 1, np.int64).copy()
-        self.db_off = _np(r.db_off, n + 1, np.int64).copy()
-        self.step_off = _np(r.step_off, n + 1, np.int64).copy()
-        self.counters = _np(r.counters, n * N.CNT_N, np.int64).reshape(n, N.CNT_N).copy()
-        self.n_struct = int(self.struct_off[n])
-        if not copy:
-            return
+        self.status = _np(r.status, n, np.int32)
+        self.struct_off = _np(r.struct_off, n + 1, np.int64)
+        self.db_off = _np(r.db_off, n + 1, np.int64)
+        self.step_off = _np(r.step_off, n + 1, np.int64)
+        self.counters = _np(r.counters, n * N.CNT_N, np.int64).reshape(n, N.CNT_N)
         nS, nD, nT = int(self.struct_off[n]), int(self.db_off[n]), int(self.step_off[n])
-        self.energy = _np(r.energy_dcal, nS, np.int32).copy()
-        self.db = C.string_at(r.db, nD) if nD else b""
-        self.entry_off = _np(r.entry_off, nT + 1, np.int64).copy()
-        self.entry_struct = _np(r.entry_struct, int(self.entry_off[nT]) if nT else 0, np.int32).copy()
+        self.n_struct = nS
+        self.energy = _np(r.energy_dcal, nS, np.int32)
+        self.db = _np(C.cast(r.db, C.POINTER(C.c_uint8)), nD, np.uint8)
+        self.entry_off = _np(r.entry_off, nT + 1, np.int64)
+        self.entry_struct = _np(r.entry_struct, int(self.entry_off[nT]) if nT else 0, np.int32)
         if offs is not None:
             self.lengths = np.diff(offs)
         else:
             ns = np.diff(self.struct_off)
             self.lengths = np.where(ns > 0, np.diff(self.db_off) // np.maximum(ns, 1), 0)
+
+    def close(self):
+        "hand the arrays back to the library; the views must not be used afterwards"
+        if self._res is not None:
+            self._lib.rafft_result_free(self._res)
+            self._res = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def steps(self, i):
         """sequence i -> list of steps, each a list of (dot-bracket, E_dcal)."""
@@ -129,7 +140,7 @@ class RawResult:
             step = []
             for e in range(int(self.entry_off[t]), int(self.entry_off[t + 1])):
                 k = int(self.entry_struct[e])
-                step.append((self.db[d0 + k * L:d0 + (k + 1) * L].decode(), int(self.energy[s0 + k])))
+                step.append((self.db[d0 + k * L:d0 + (k + 1) * L].tobytes().decode(), int(self.energy[s0 + k])))
             out.append(step)
         return out
 

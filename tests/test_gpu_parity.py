@@ -186,7 +186,7 @@ def test_full_batch_properties(ctx):
     assert (got == np.array(ev_e, dtype=np.int32)).all()
     # determinism / idempotence
     raw2 = ctx.fold_raw("".join(seqs).encode(), offs, R.make_params(100, 50, 1000, traj=False))
-    assert raw2.db == raw.db and (raw2.energy == raw.energy).all()
+    assert (raw2.db == raw.db).all() and (raw2.energy == raw.energy).all()
 
 
 # ---- the drop-in surface ---------------------------------------------------------------
