@@ -140,6 +140,19 @@ int rafft_fold_batch_device(rafft_ctx *ctx, const void *d_seqs, const void *d_of
 int rafft_eval_structures(rafft_ctx *ctx, const char *seqs, const char *structs,
                           const int64_t *offs, int32_t n, int32_t *energy_dcal);
 
+/* Folding graph of the kinetics (reference rafft/rafft_kin.py:48-56 get_connected_prev, :106-115
+ * the non-redundant numbering in kinetics).  db: n = step_off[n_steps] dot-bracket rows of L
+ * characters, the folding steps concatenated (the blocks of a `rafft --traj` output).
+ *   uniq[i]   index of the first row equal to row i (struct_map of the reference)
+ *   conn      for step t, for every structure c of step t and every structure p of step t-1
+ *             (step 0 looks at the LAST step: fast_paths[-1], rafft_kin.py:75), 1 iff every pair of
+ *             p is a pair of c; the row of c starts at conn_off[t] + (c - step_off[t]) * n_prev
+ *   conn_off  n_steps + 1 offsets into conn (written by the call); conn_cap = capacity of conn
+ * A closing bracket without partner is RAFFT_ERR_SEQ (the reference raises IndexError,
+ * rafft/utils.py:62-65). */
+int rafft_kin_graph(rafft_ctx *ctx, const char *db, int32_t L, const int64_t *step_off, int32_t n_steps,
+                    int32_t *uniq, uint8_t *conn, int64_t conn_cap, int64_t *conn_off);
+
 /* Library/build identification, e.g. "rafft_b200 0.1 sm_100a". */
 const char *rafft_version(void);
 

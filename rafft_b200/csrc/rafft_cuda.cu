@@ -21,6 +21,7 @@
 #include <vector>
 #include "host_common.h"
 #include "expand_fast.cuh"
+#include "kin_cuda.cuh"
 
 using namespace rafft;
 
@@ -395,7 +396,7 @@ struct rafft_ctx {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, evx0 = nullptr, evx1 = nullptr;
   DevEnergy *d_energy = nullptr;
-  DevBuf arenas, seqs, offs, order, subset, idx, big, ordered, scan, evalbuf, states, tasks, ftasks, scratch, small;
+  DevBuf arenas, seqs, offs, order, subset, idx, big, ordered, scan, evalbuf, states, tasks, ftasks, scratch, small, kinbuf;
   std::vector<HostBlock> pinned_free;
   int64_t *h_small = nullptr; /* pinned: totals + cursors */
   int block_threads = 64;   /* threads per block of the block-scope phase kernels */
@@ -482,7 +483,7 @@ void rafft_destroy(rafft_ctx *ctx) {
   cudaSetDevice(ctx->device);
   DevBuf *bufs[] = {&ctx->arenas, &ctx->seqs, &ctx->offs, &ctx->order, &ctx->subset, &ctx->idx,
                     &ctx->states, &ctx->tasks, &ctx->ftasks, &ctx->scratch, &ctx->small,
-                    &ctx->big, &ctx->ordered, &ctx->scan, &ctx->evalbuf};
+                    &ctx->big, &ctx->ordered, &ctx->scan, &ctx->evalbuf, &ctx->kinbuf};
   for (DevBuf *b : bufs)
     if (b->p) cudaFree(b->p);
   for (auto &b : ctx->pinned_free) cudaFreeHost(b.p);
@@ -965,6 +966,60 @@ int rafft_eval_structures(rafft_ctx *ctx, const char *seqs, const char *structs,
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(energy_dcal, d + o_e, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
+  return RAFFT_OK;
+}
+
+int rafft_kin_graph(rafft_ctx *ctx, const char *db, int32_t L, const int64_t *step_off, int32_t n_steps,
+                    int32_t *uniq, uint8_t *conn, int64_t conn_cap, int64_t *conn_off) {
+  if (!ctx) return RAFFT_ERR_ARG;
+  if (n_steps < 0 || L < 1 || L > 32767 || !step_off || !conn_off || (n_steps > 0 && (!db || !uniq))) {
+    ctx->err = "rafft_kin_graph: bad argument";
+    return RAFFT_ERR_ARG;
+  }
+  for (int t = 0; t < n_steps; t++)
+    if (step_off[t + 1] < step_off[t] || step_off[0] != 0) { ctx->err = "rafft_kin_graph: bad step offsets"; return RAFFT_ERR_ARG; }
+  const int64_t n = n_steps ? step_off[n_steps] : 0;
+  conn_off[0] = 0;
+  for (int t = 0; t < n_steps; t++) {
+    const int tp = t == 0 ? n_steps - 1 : t - 1;
+    conn_off[t + 1] = conn_off[t] + (step_off[t + 1] - step_off[t]) * (step_off[tp + 1] - step_off[tp]);
+  }
+  const int64_t total = conn_off[n_steps];
+  if (n == 0) return RAFFT_OK;
+  if (n > 0x7fffffff / 2) { ctx->err = "rafft_kin_graph: too many structures"; return RAFFT_ERR_ARG; }
+  if (total > conn_cap || (total > 0 && !conn)) { ctx->err = "rafft_kin_graph: conn buffer too small"; return RAFFT_ERR_ARG; }
+  CK(cudaSetDevice(ctx->device));
+  /* db | pt | stacks | hash | bad | uniq | step_off | conn_off | conn */
+  size_t o_db = 0, o_pt = align_up((size_t)n * L, 256), o_st = align_up(o_pt + sizeof(int16_t) * (size_t)n * L, 256),
+         o_hash = align_up(o_st + sizeof(int16_t) * 2 * (size_t)n * L, 256), o_bad = o_hash + sizeof(uint64_t) * (size_t)n,
+         o_uniq = o_bad + sizeof(int32_t) * (size_t)n, o_so = align_up(o_uniq + sizeof(int32_t) * (size_t)n, 256),
+         o_co = o_so + sizeof(int64_t) * (size_t)(n_steps + 1), o_conn = align_up(o_co + sizeof(int64_t) * (size_t)(n_steps + 1), 256),
+         o_end = o_conn + (size_t)total + 16;
+  if (int rc = dev_reserve(ctx, ctx->kinbuf, o_end)) return rc;
+  char *d = (char *)ctx->kinbuf.p;
+  CK(cudaMemcpyAsync(d + o_db, db, (size_t)n * L, cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(d + o_so, step_off, sizeof(int64_t) * (size_t)(n_steps + 1), cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(d + o_co, conn_off, sizeof(int64_t) * (size_t)(n_steps + 1), cudaMemcpyHostToDevice, ctx->stream));
+  const int wpb = 4;
+  kin_pairtable_kernel<<<(unsigned)((n + wpb - 1) / wpb), wpb * 32, 0, ctx->stream>>>(
+      d + o_db, (int)n, L, (int16_t *)(d + o_pt), (int16_t *)(d + o_st), (uint64_t *)(d + o_hash), (int32_t *)(d + o_bad));
+  kin_unique_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(d + o_db, (const uint64_t *)(d + o_hash), (int)n, L,
+                                                                         (int32_t *)(d + o_uniq));
+  if (total > 0) {
+    const int64_t blocks = (total + wpb - 1) / wpb;
+    if (blocks > 0x7fffffff) { ctx->err = "rafft_kin_graph: graph too large"; return RAFFT_ERR_ARG; }
+    kin_connect_kernel<<<(unsigned)blocks, wpb * 32, 0, ctx->stream>>>((const int16_t *)(d + o_pt), (const int64_t *)(d + o_so),
+                                                                     (const int64_t *)(d + o_co), n_steps, L,
+                                                                     (uint8_t *)(d + o_conn), total);
+  }
+  CK(cudaGetLastError());
+  std::vector<int32_t> bad((size_t)n);
+  CK(cudaMemcpyAsync(bad.data(), d + o_bad, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(uniq, d + o_uniq, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  if (total > 0) CK(cudaMemcpyAsync(conn, d + o_conn, (size_t)total, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  for (int64_t i = 0; i < n; i++)
+    if (bad[(size_t)i]) { ctx->err = "rafft_kin_graph: closing bracket without partner in structure " + std::to_string(i); return RAFFT_ERR_SEQ; }
   return RAFFT_OK;
 }
 
