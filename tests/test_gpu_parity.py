@@ -206,3 +206,54 @@ def test_fold_api_like_reference(ctx):
     assert [s.str_struct for s in final] == [db for db, _ in gold[-1]]
     assert ["%6.1f" % s.energy for s in traj[1]] == ["%6.1f" % float(e) for _, e in gold[1]]
     assert isinstance(fold(seq), list) and len(fold(seq)) == 1
+
+
+# ---- the BASELINE.json configurations at their own parameters ------------------------------
+def test_cfg1_single_120nt(ctx, oracle):
+    "configs[0]: one synthetic 120-nt RNA, -n 100 -ms 50 --traj, against the CPU run of the oracle"
+    s = splitmix_seq(1, 120)
+    got, _ = gpu_steps(ctx, [s], nb_mode=100, max_stack=50)
+    assert got[0] == oracle.fold(s, 100, 50, 1000)
+
+
+def test_cfg3_full_batch_properties(ctx):
+    "configs[2] at full size (10k sequences, -n 200 -ms 200): invariants + energies re-derived"
+    from rafft_b200 import rafft as R
+    seqs = config_batch("cfg2")
+    offs = np.zeros(len(seqs) + 1, dtype=np.int64)
+    np.cumsum([len(s) for s in seqs], out=offs[1:])
+    raw = ctx.fold_raw("".join(seqs).encode(), offs, R.make_params(200, 200, 1000, traj=False))
+    assert (raw.status == 0).all()
+    ns = np.diff(raw.struct_off)
+    assert (ns >= 1).all() and (ns <= 200).all()
+    ev_s, ev_d, ev_e = [], [], []
+    for i in range(0, len(seqs), 41):
+        final = raw.steps(i)[-1]
+        es = [e for _, e in final]
+        assert es == sorted(es) and len(set(db for db, _ in final)) == len(final)
+        for db, e in final[::5]:
+            assert len(db) == len(seqs[i]) and db.count("(") == db.count(")")
+            ev_s.append(seqs[i]); ev_d.append(db); ev_e.append(e)
+    got = ctx.eval_structures(ev_s, ev_d)
+    assert (got == np.array(ev_e, dtype=np.int32)).all()
+
+
+def test_cfg4_3000nt_vs_oracle(ctx, oracle):
+    "configs[3] parameters (-n 200 -ms 200) on 3,000-nt inputs: bit-exact against the oracle"
+    seqs = [splitmix_seq(3000 + k, 3000) for k in range(2)]
+    got, _ = gpu_steps(ctx, seqs, nb_mode=200, max_stack=200)
+    want = oracle.fold_batch(seqs, 200, 200, 1000)[0]
+    assert got == want
+
+
+def test_cfg5_fold_then_kinetics(ctx, oracle):
+    "configs[4]: 200-nt RNA at -ms 200 --traj, the GPU-built trajectory fed to the kinetics"
+    from rafft_b200 import rafft as R, rafft_kin as K
+    s = splitmix_seq(200, 200)
+    final, traj = R.fold_batch([s], 100, 200, 1000, traj=True, context=ctx)[0]
+    want = oracle.fold(s, 100, 200, 1000)
+    assert [[(st.str_struct, st.energy_dcal) for st in step] for step in traj] == want
+    pops, times, struct_list, equi = K.kinetics(traj, 30, 100)
+    assert len(times) == 101 and len(struct_list) == len({st.str_struct for step in traj for st in step})
+    early = np.asarray(pops[50], dtype=np.float64)
+    assert abs(early.sum() - 1.0) < 1e-9 and early.min() > -1e-6
