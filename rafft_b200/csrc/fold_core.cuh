@@ -474,7 +474,9 @@ struct SeqState {
   int32_t n_node, n_pool16, n_cand, n_store, n_nlist, n_seen, n_todo, n_expand;
   int32_t beam_n, n_new, nb_branch, n_steps, n_traj;
   int32_t tmp0, tmp1, tmp2, cur_b, xcut;
-  int32_t fail_line, pad0_; /* source line of the first capacity failure (diagnostics) */
+  int32_t fail_line;       /* source line of the first capacity failure (diagnostics) */
+  int32_t exp_from;        /* loop records from this id on may still need their expansion */
+  int32_t qcnt[8], qbase[8]; /* gather: regions per work list (6 size classes + generic) */
   int32_t emin, emax, cnt_le;
   int32_t wsum[12];
   int64_t seq_off;         /* first letter of the sequence in the batch text */
@@ -1109,7 +1111,7 @@ struct Fold {
       sh->n_node = 0; sh->n_pool16 = 0; sh->n_cand = 0; sh->n_store = 0; sh->n_nlist = 0;
       sh->n_seen = 0; sh->n_todo = 0; sh->n_expand = 0; sh->beam_n = 0; sh->n_new = 0;
       sh->nb_branch = 0; sh->n_steps = 0; sh->n_traj = 0;
-      sh->active = 1; sh->stage = 0; sh->expand_pending = 0; sh->fail_line = 0;
+      sh->active = 1; sh->stage = 0; sh->expand_pending = 0; sh->fail_line = 0; sh->exp_from = 0;
       for (int k = 0; k < CNT_N; k++) sh->cnt[k] = 0;
       sh->cnt[CNT_T0_NS] = (unsigned long long)Exec::now_ns();
       if (L > caps.L_max) sh->status = ST_ERR_CAPACITY;
@@ -1184,27 +1186,49 @@ struct Fold {
         sh->stage = 1;
       }
       sh->expand_pending = 0;
+      for (int c = 0; c < 8; c++) sh->qcnt[c] = 0;
     RF_SINGLE_END
     if (sh->status != ST_OK) { finish_fold(); return; }
-    /* P1: the loops of the beam that have not been expanded yet become warp tasks */
-    RF_PAR_BEGIN(b, beam_n)
-      const StoreRec &S = A.store[A.beam[b]];
-      if (!S.done) {
-        for (int k = 0; k < S.nl_n; k++) {
-          int v = A.nlist[S.nl_off + k];
-          if (A.node[v].cand_n == -1 && Exec::atomic_cas(&A.node[v].cand_n, -1, -2) == -1) {
-            const bool fast = Q.fast_cap > 0 && A.node[v].lv <= Q.fast_lv && A.node[v].br_n <= Q.fast_br;
-            int cls = 0;
-            while ((32 << cls) < 2 * A.node[v].lv - 1) cls++;
-            int32_t *list = fast ? Q.fast_task + 2 * (size_t)cls * (size_t)Q.fast_cap : Q.task;
-            const int cap = fast ? Q.fast_cap : Q.cap;
-            int at = Exec::atomic_add(fast ? Q.n_fast + cls : Q.n_tasks, 1);
-            if (at < cap) { list[2 * at] = Q.self; list[2 * at + 1] = v; }
-            else { A.node[v].cand_n = -1; sh->expand_pending = 1; } /* next round */
-          }
-        }
+    /* P1: the loops that have not been expanded yet become warp tasks.  They are exactly the loop
+     * records created since the last gather that are the first of their kind (every new record
+     * belongs to a child that was selected into the beam); one global reservation per work list
+     * and block instead of one atomic per region. */
+    const int from = sh->exp_from, n_new_nodes = sh->n_node - from;
+#define RF_GATHER_CLASS(nd, cls)                                                              \
+  int cls = RF_FAST_CLASSES;                                                                  \
+  if (Q.fast_cap > 0 && (nd).lv <= Q.fast_lv && (nd).br_n <= Q.fast_br) {                     \
+    cls = 0;                                                                                  \
+    while ((32 << cls) < 2 * (nd).lv - 1) cls++;                                              \
+  }
+    RF_PAR_BEGIN(x, n_new_nodes)
+      const NodeRec &nd = A.node[from + x];
+      if (nd.nht_slot >= 0 && nd.cand_n == -1) {
+        RF_GATHER_CLASS(nd, cls)
+        Exec::atomic_add(&sh->qcnt[cls], 1);
       }
     RF_PAR_END
+    RF_SINGLE_BEGIN
+      for (int c = 0; c <= RF_FAST_CLASSES; c++) {
+        if (sh->qcnt[c]) sh->qbase[c] = Exec::atomic_add(c < RF_FAST_CLASSES ? Q.n_fast + c : Q.n_tasks, sh->qcnt[c]);
+        sh->qcnt[c] = 0;
+      }
+    RF_SINGLE_END
+    RF_PAR_BEGIN(x, n_new_nodes)
+      NodeRec &nd = A.node[from + x];
+      if (nd.nht_slot >= 0 && nd.cand_n == -1) {
+        RF_GATHER_CLASS(nd, cls)
+        const bool fast = cls < RF_FAST_CLASSES;
+        int32_t *list = fast ? Q.fast_task + 2 * (size_t)cls * (size_t)Q.fast_cap : Q.task;
+        const int cap = fast ? Q.fast_cap : Q.cap;
+        const int at = sh->qbase[cls] + Exec::atomic_add(&sh->qcnt[cls], 1);
+        if (at < cap) { list[2 * at] = Q.self; list[2 * at + 1] = from + x; nd.cand_n = -2; }
+        else sh->expand_pending = 1; /* next round */
+      }
+    RF_PAR_END
+#undef RF_GATHER_CLASS
+    RF_SINGLE_BEGIN
+      if (!sh->expand_pending) sh->exp_from = sh->n_node;
+    RF_SINGLE_END
   }
 
   /* ---- phase: combine stems of independent regions (rafft.py:176-203) */
