@@ -117,7 +117,7 @@ struct OutBuf {
   int32_t *status;      /* per sequence */
   int64_t *seq_struct;  /* per sequence: first structure index */
   int32_t *seq_nstruct;
-  int64_t *seq_db;      /* per sequence: first db byte */
+  int64_t *seq_db;      /* per sequence: first db byte (rows padded to 16 bytes, 16-byte aligned) */
   int64_t *seq_step;    /* per sequence: first step index */
   int32_t *seq_nstep;
   int64_t *seq_entry;   /* per sequence: first entry index */
@@ -449,6 +449,8 @@ struct Arena {
   int32_t *todo;       /* todo_cap * 3 */
   int32_t *todo_id;    /* todo_cap */
   int32_t *flag, *pref; /* sel_cap = max(chunk_cap, new_cap + max_stack) */
+  int32_t *sel_e;       /* sel_cap: energies of the entries under selection (the select kernel
+                           points this at shared memory when they fit) */
 };
 
 /* Scratch of one node expansion (views into the warp's slice of Arena::wscratch). */
@@ -555,12 +557,13 @@ RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &
   RF_CARVE(todo_id, int32_t, c.todo_cap);
   RF_CARVE(flag, int32_t, sel_cap);
   RF_CARVE(pref, int32_t, sel_cap);
+  RF_CARVE(sel_e, int32_t, sel_cap);
 #undef RF_CARVE
   return align_up(off, 256);
 }
 /* Byte offsets of the arena pieces (computed once on the host, bound per block/warp). */
 struct ArenaOff {
-  uint32_t seen, nht, code, node, pool16, cand, store, store_db, nlist, ncnt, seen_used, fresh, sel, sel_idx, sel_store, beam, traj_n, traj, todo, todo_id, flag, pref;
+  uint32_t seen, nht, code, node, pool16, cand, store, store_db, nlist, ncnt, seen_used, fresh, sel, sel_idx, sel_store, beam, traj_n, traj, todo, todo_id, flag, pref, sel_e;
 };
 RF_HD void arena_bind(Arena &A, char *base, const ArenaOff &o) {
   A.seen = (SeenEnt *)(base + o.seen);
@@ -585,6 +588,7 @@ RF_HD void arena_bind(Arena &A, char *base, const ArenaOff &o) {
   A.todo_id = (int32_t *)(base + o.todo_id);
   A.flag = (int32_t *)(base + o.flag);
   A.pref = (int32_t *)(base + o.pref);
+  A.sel_e = (int32_t *)(base + o.sel_e);
 }
 #ifndef __CUDACC_RTC__
 inline void arena_offsets(ArenaOff &o, const Caps &c, const FoldParams &fp) {
@@ -613,6 +617,7 @@ inline void arena_offsets(ArenaOff &o, const Caps &c, const FoldParams &fp) {
   o.todo_id = (uint32_t)((char *)A.todo_id - base);
   o.flag = (uint32_t)((char *)A.flag - base);
   o.pref = (uint32_t)((char *)A.pref - base);
+  o.sel_e = (uint32_t)((char *)A.sel_e - base);
 }
 #endif
 /* bytes at the start of an arena that hold the hash tables (zeroed by the host once) */
@@ -1149,10 +1154,21 @@ struct Fold {
   RF_FN void phase_finish(OutBuf &out) {
     emit(out);
     /* leave the two hash tables empty for the next sequence of this arena */
-    RF_PAR_BEGIN(i, sh->n_seen)
-      A.seen[A.seen_used[i]].lo = 0;
-      A.seen[A.seen_used[i]].hi = 0;
-    RF_PAR_END
+    {
+      /* four independent slot look-ups in flight per thread */
+      const int n_seen = sh->n_seen;
+      Exec::sync();
+      for (int i = Exec::tid(); i < n_seen; i += 4 * Exec::stride()) {
+        int idx[4];
+        for (int q = 0; q < 4; q++) {
+          const int j = i + q * Exec::stride();
+          idx[q] = j < n_seen ? A.seen_used[j] : -1;
+        }
+        for (int q = 0; q < 4; q++)
+          if (idx[q] >= 0) { A.seen[idx[q]].lo = 0; A.seen[idx[q]].hi = 0; }
+      }
+      Exec::sync();
+    }
     RF_PAR_BEGIN(i, sh->n_node)
       int s = A.node[i].nht_slot;
       if (s >= 0) A.nht[s] = 0;
@@ -1425,7 +1441,11 @@ struct Fold {
     const int n_new = sh->n_new;
     const int total = n_new + beam_n;
     const int keep = total < prm.max_stack ? total : prm.max_stack;
-#define RF_ENTRY_E(i) ((i) < n_new ? A.fresh[(i)].e : A.store[A.beam[(i) - n_new]].e)
+    /* the energies once, side by side (the bisection below reads them ~16 times) */
+    RF_PAR_BEGIN(i, total)
+      A.sel_e[i] = i < n_new ? A.fresh[i].e : A.store[A.beam[i - n_new]].e;
+    RF_PAR_END
+#define RF_ENTRY_E(i) (A.sel_e[(i)])
     if (total > keep) {
       RF_SINGLE_BEGIN
         sh->emin = 0x7fffffff; sh->emax = (int)0x80000000;
@@ -1668,10 +1688,11 @@ struct Fold {
         }
       }
       unsigned long long s0 = Exec::atomic_add64(&out.cursors[0], (unsigned long long)nstruct);
-      unsigned long long d0 = Exec::atomic_add64(&out.cursors[1], (unsigned long long)nstruct * L);
+      const unsigned long long Lp = (unsigned long long)db_stride();
+      unsigned long long d0 = Exec::atomic_add64(&out.cursors[1], (unsigned long long)nstruct * Lp);
       unsigned long long t0 = Exec::atomic_add64(&out.cursors[2], (unsigned long long)nstep);
       unsigned long long e0 = Exec::atomic_add64(&out.cursors[3], (unsigned long long)nentry);
-      if ((int64_t)(s0 + nstruct) > out.struct_cap || (int64_t)(d0 + (uint64_t)nstruct * L) > out.db_cap ||
+      if ((int64_t)(s0 + nstruct) > out.struct_cap || (int64_t)(d0 + (uint64_t)nstruct * Lp) > out.db_cap ||
           (int64_t)(t0 + nstep) > out.step_cap || (int64_t)(e0 + nentry) > out.entry_cap) {
         if (sh->status == ST_OK) sh->status = ST_ERR_CAPACITY;
         nstruct = nstep = nentry = 0;
@@ -1695,9 +1716,9 @@ struct Fold {
       RF_PAR_END
       Exec::sync();
       for (int k = Exec::warp(); k < nstruct; k += Exec::nwarps()) {
-        const char *src = db_row(k);
-        char *dst = out.db + d0 + (int64_t)k * L;
-        for (int b = Exec::lane(); b < L; b += Exec::lanes()) dst[b] = src[b];
+        const Vec16 *src = (const Vec16 *)db_row(k);
+        Vec16 *dst = (Vec16 *)(out.db + d0 + (int64_t)k * db_stride());
+        for (int w = Exec::lane(); w < (db_stride() >> 4); w += Exec::lanes()) dst[w] = src[w];
       }
       Exec::sync();
       RF_SINGLE_BEGIN
@@ -1714,9 +1735,9 @@ struct Fold {
       RF_PAR_END
       Exec::sync();
       for (int k = Exec::warp(); k < nstruct; k += Exec::nwarps()) {
-        const char *src = db_row(A.beam[k]);
-        char *dst = out.db + d0 + (int64_t)k * L;
-        for (int b = Exec::lane(); b < L; b += Exec::lanes()) dst[b] = src[b];
+        const Vec16 *src = (const Vec16 *)db_row(A.beam[k]);
+        Vec16 *dst = (Vec16 *)(out.db + d0 + (int64_t)k * db_stride());
+        for (int w = Exec::lane(); w < (db_stride() >> 4); w += Exec::lanes()) dst[w] = src[w];
       }
       Exec::sync();
       RF_SINGLE_BEGIN

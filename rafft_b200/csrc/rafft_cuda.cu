@@ -66,6 +66,7 @@ struct WaveCtx {
   TaskQueue Q;
   FastCfg fast;
   int32_t *fast_next; /* dynamic work counter of k_expand_fast */
+  int32_t sel_smem;   /* bytes of shared memory for the energies under selection (0: global) */
   int32_t *n_active;
   OutBuf out;
 };
@@ -128,7 +129,9 @@ __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_combine(RF_WAVE_PARAM)
 __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_select(RF_WAVE_PARAM) {
   __shared__ SeqState sh;
   Fold f(c.E, c.prm, c.caps);
+  extern __shared__ __align__(16) char select_smem[];
   if (!BlockBind::load(c, f, &sh, true)) return;
+  if (c.sel_smem) f.A.sel_e = (int32_t *)select_smem;
   f.phase_select();
   BlockBind::store(c, &sh);
 }
@@ -293,7 +296,12 @@ __global__ void pack_kernel(const int64_t *__restrict__ offs, int n, OutBuf out,
   const int64_t s_dst = struct_off[i], d_dst = db_off[i], t_dst = step_off[i], e_dst = ent_base[i];
   for (int k = threadIdx.x; k < ns; k += blockDim.x) energy[s_dst + k] = out.energy[s_src + k];
   const int64_t nbytes = (int64_t)ns * L;
-  for (int64_t k = threadIdx.x; k < nbytes; k += blockDim.x) db[d_dst + k] = out.db[d_src + k];
+  /* source rows are padded to 16 bytes (fold_core.cuh db_stride), the result is compact */
+  const int64_t Lp = (L + 15) & ~(int64_t)15;
+  for (int64_t k = threadIdx.x; k < nbytes; k += blockDim.x) {
+    const int64_t r = k / L;
+    db[d_dst + k] = out.db[d_src + r * Lp + (k - r * L)];
+  }
   const int64_t ne = ent_base[i + 1] - e_dst;
   for (int64_t k = threadIdx.x; k < ne; k += blockDim.x) entry_struct[e_dst + k] = out.entries[e_src + k];
   if (threadIdx.x == 0) {
@@ -660,7 +668,7 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     else for (int i : todo) sum_L += h_offs[i + 1] - h_offs[i];
     OutBuf N = O;
     N.struct_cap = used[0] + per_struct * m;
-    N.db_cap = used[1] + per_struct * sum_L;
+    N.db_cap = used[1] + per_struct * (sum_L + 15 * (int64_t)m); /* rows padded to 16 bytes */
     N.step_cap = used[2] + per_step * m;
     N.entry_cap = used[3] + (F.traj ? per_step * F.max_stack : (int64_t)F.max_stack) * m;
     size_t big_bytes = big_layout(N, nullptr);
@@ -749,6 +757,10 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     CombineStage cs_probe;
     const size_t stage_bytes = stage_carve(cs_probe, nullptr, caps.chunk_cap, F.max_stack);
     CK(cudaFuncSetAttribute(k_combine, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stage_bytes));
+    {
+      const size_t sel_bytes = sizeof(int32_t) * (size_t)std::max<int64_t>(caps.chunk_cap, (int64_t)caps.new_cap + F.max_stack);
+      wc.sel_smem = sel_bytes <= 40 * 1024 ? (int32_t)sel_bytes : 0;
+    }
     const int egrid = ctx->sm_count * ctx->blocks_per_sm;
     if (fcap > 0) CK(cudaFuncSetAttribute(fsh.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast_smem));
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
@@ -779,7 +791,7 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
           launches += 5;
         }
         k_combine<<<nw, T, stage_bytes, ctx->stream>>>(wc);
-        k_select<<<nw, T, 0, ctx->stream>>>(wc);
+        k_select<<<nw, T, (size_t)wc.sel_smem, ctx->stream>>>(wc);
         k_materialise<<<nw, T, 0, ctx->stream>>>(wc);
         launches += 3;
         CK(cudaMemcpyAsync(ctx->h_small + 16, (int32_t *)ctx->small.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
@@ -795,7 +807,7 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
         if (hs[1] == 0) break;
         if (it > 100000) { ctx->err = "rafft_fold_batch: no progress"; return fail(RAFFT_ERR_CUDA); }
       }
-      k_finish<<<nw, T, 0, ctx->stream>>>(wc);
+      k_finish<<<nw, RF_BLOCK_THREADS_MAX, 0, ctx->stream>>>(wc);
       launches++;
     }
     CK(cudaEventRecord(ctx->ev1, ctx->stream));

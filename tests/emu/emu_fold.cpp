@@ -59,7 +59,7 @@ int emu_fold(const rafft_energy_params *ep_in, const char *seq, int L, const raf
   int64_t scap = (int64_t)caps.store_cap, ecap = (int64_t)caps.step_cap * F.max_stack;
   std::vector<int32_t> status(1), nstruct(1), nstep(1), energy(scap), step_n(caps.step_cap), entries(ecap);
   std::vector<int64_t> sstruct(1), sdb(1), sstep(1), sentry(1), counters(CNT_N);
-  std::vector<char> db((size_t)scap * (L > 0 ? L : 1));
+  std::vector<char> db((size_t)scap * (size_t)(((L > 0 ? L : 1) + 15) & ~15) + 16);
   unsigned long long cursors[8] = {0};
   OutBuf out;
   out.status = status.data(); out.seq_struct = sstruct.data(); out.seq_nstruct = nstruct.data();
@@ -104,7 +104,7 @@ int emu_fold(const rafft_energy_params *ep_in, const char *seq, int L, const raf
       o += buf;
       for (int b = 0; b < step_n[sstep[0] + s]; b++, e++) {
         int k = entries[e];
-        o.append(db.data() + sdb[0] + (size_t)k * L, L);
+        o.append(db.data() + sdb[0] + (size_t)k * (size_t)((L + 15) & ~15), L);
         snprintf(buf, sizeof buf, " %d\n", energy[sstruct[0] + k]);
         o += buf;
       }
