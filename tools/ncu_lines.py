@@ -43,13 +43,14 @@ print("sass rows: ncu %d, nvdisasm %d" % (len(data), len(insts)))
 n = min(len(data), len(insts))
 mism = sum(1 for k in range(n) if data[k]["Source"].split()[0].lstrip("@!P0123456789T ") [:3] != insts[k][1].split()[0].lstrip("@!P0123456789T ")[:3])
 print("opcode mismatches:", mism)
-agg = collections.defaultdict(lambda: [0, 0, collections.Counter()])
+agg = collections.defaultdict(lambda: [0, 0, collections.Counter(), 0])
 stall_cols = [h for h in H if h.startswith("stall_")]
 for k in range(n):
     d = data[k]
     a = agg[insts[k][0]]
     a[0] += int(d["Instructions Executed"] or 0)
     a[1] += int(d["# Samples"] or 0)
+    a[3] += int(d.get("Predicated-On Thread Instructions Executed") or 0)
     for s in stall_cols:
         v = int(d[s] or 0)
         if v:
@@ -58,5 +59,5 @@ ti = sum(a[0] for a in agg.values()); ts = sum(a[1] for a in agg.values())
 print("total warp inst %d, samples %d" % (ti, ts))
 print("--- by samples")
 for key, a in sorted(agg.items(), key=lambda kv: -kv[1][1])[:top]:
-    print("%-22s inst %6.2f%%  samples %6.2f%%  %s" % ("%s:%d" % key if key else "?", 100.0 * a[0] / ti, 100.0 * a[1] / ts,
+    print("%-22s inst %6.2f%%  samples %6.2f%%  thr %5.1f  %s" % ("%s:%d" % key if key else "?", 100.0 * a[0] / ti, 100.0 * a[1] / ts, a[3] / max(a[0], 1),
                                                   " ".join("%s=%d" % kv for kv in a[2].most_common(3))))
