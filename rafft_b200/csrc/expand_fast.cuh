@@ -38,7 +38,6 @@ struct FastCfg {
   int32_t o_mask, o_pos, o_brcnt, o_lcode, o_pre, o_rlag, o_A; /* byte offsets in the warp slice */
   int32_t o_stem, o_ck, o_nb;                                  /* pieces of A after the ranking */
   int32_t o_wst;                                               /* 4 ints of warp state */
-  int32_t o_order;                                             /* scan order of the ranked lags */
 };
 
 #ifndef __CUDACC_RTC__
@@ -68,7 +67,6 @@ inline bool build_fast_cfg(FastCfg &fc, int L_max, const FoldParams &F) {
   fc.o_pre = carve(4 * 2 * (size_t)(fc.br_cap + 1));
   fc.o_rlag = carve(2 * (size_t)nr);
   fc.o_wst = carve(16);
-  fc.o_order = carve((size_t)nr);
   size_t a_keys = 4 * (size_t)nk_cap;
   size_t a_after = 4 * (size_t)nr + 4 * (size_t)ck_cap + 2 * (size_t)nr + 32;
   fc.o_A = carve(a_keys > a_after ? a_keys : a_after);
@@ -245,13 +243,12 @@ __device__ __forceinline__ int fast_stem_dE(const FastTask &T, const EnergyView 
   uint32_t *ck = (uint32_t *)(ws + fc.o_ck);                                                    \
   uint16_t *r_nb = (uint16_t *)(ws + fc.o_nb);                                                  \
   int32_t *wst = (int32_t *)(ws + fc.o_wst); /* keep_n, n_pos, w_scan */                        \
-  uint8_t *order = (uint8_t *)(ws + fc.o_order);                                                \
   const int nlag = 2 * lv - 1;                                                                  \
   const int nr = nlag < prm.nb_mode ? nlag : prm.nb_mode;                                       \
   const unsigned FULL = 0xffffffffu;                                                            \
   (void)code; (void)br; (void)ci; (void)cj; (void)m; (void)FH; (void)FL; (void)RH; (void)RL; (void)CL; (void)CLR;     \
   (void)pos; (void)brcnt; (void)lcode; (void)pre_ml; (void)pre_ext; (void)rlag; (void)keys;     \
-  (void)r_stem; (void)ck; (void)r_nb; (void)wst; (void)nr; (void)FULL; (void)order;
+  (void)r_stem; (void)ck; (void)r_nb; (void)wst; (void)nr; (void)FULL;
 
 #define RF_FAST_ARGS                                                                            \
   const DevEnergy *E, const FoldParams &prm, const Caps &caps, const FastCfg &fc, char *arena,  \
@@ -364,52 +361,6 @@ __device__ __forceinline__ void fast_p4(RF_FAST_ARGS) {
     const int r = K * lane + q;
     if (r < nr) rlag[r] = (uint16_t)(vreg[q] & ((1u << RF_FAST_LAGBITS) - 1));
   }
-  __syncwarp();
-  /* Scan order of the ranked lags: by the number of 32-position words their half anti-diagonal
-   * touches, longest first.  The scan of phase 5 gives a lag to every lane; lanes of one round
-   * then have the same amount of work and the incomplete last round holds the shortest lags
-   * (the results stay indexed by rank, so the order is invisible outside). */
-  constexpr int MW = K <= 2 ? 2 : K == 4 ? 2 : K == 8 ? 3 : K == 16 ? 5 : 9;
-  int cnt[MW + 1];
-#pragma unroll
-  for (int b = 0; b <= MW; b++) cnt[b] = 0;
-  for (int r0 = 0; r0 < nr; r0 += 32) {
-    const int r = r0 + lane;
-    int nwd = 0;
-    if (r < nr) {
-      const int p = rlag[r];
-      const int i0 = p < lv ? 0 : p - lv + 1;
-      const int d = p < lv ? p + 1 : 2 * lv - 1 - p;
-      nwd = ((i0 + ((d + 1) >> 1) - 1) >> 5) - (i0 >> 5) + 1;
-      nwd = nwd > MW ? MW : nwd;
-    }
-#pragma unroll
-    for (int b = 1; b <= MW; b++) cnt[b] += __popc(__ballot_sync(FULL, nwd == b));
-  }
-  /* first slot of bucket b when the buckets are laid out MW, MW-1, ..., 1 */
-  int off[MW + 1];
-  {
-    int run = 0;
-#pragma unroll
-    for (int b = MW; b >= 1; b--) { off[b] = run; run += cnt[b]; }
-  }
-  for (int r0 = 0; r0 < nr; r0 += 32) {
-    const int r = r0 + lane;
-    int nwd = 0;
-    if (r < nr) {
-      const int p = rlag[r];
-      const int i0 = p < lv ? 0 : p - lv + 1;
-      const int d = p < lv ? p + 1 : 2 * lv - 1 - p;
-      nwd = ((i0 + ((d + 1) >> 1) - 1) >> 5) - (i0 >> 5) + 1;
-      nwd = nwd > MW ? MW : nwd;
-    }
-#pragma unroll
-    for (int b = 1; b <= MW; b++) {
-      const unsigned bal = __ballot_sync(FULL, nwd == b);
-      if (nwd == b) order[off[b] + __popc(bal & ((1u << lane) - 1))] = (uint8_t)r;
-      off[b] += __popc(bal);
-    }
-  }
 }
 
 /* phase 5: per ranked lag the best consecutive stem (window_slide, rafft.py:36-83) over the set
@@ -419,8 +370,7 @@ __device__ __forceinline__ void fast_p5(RF_FAST_ARGS) {
   const double dGC = prm.w[1][2], dAU = prm.w[0][3], dGU = prm.w[2][3];
   const unsigned mGC = dGC == 0.0 ? 0u : FULL, mAU = dAU == 0.0 ? 0u : FULL, mGU = dGU == 0.0 ? 0u : FULL;
   int w_scan = 0;
-  for (int x = lane; x < nr; x += 32) {
-    const int r = order[x];
+  for (int r = lane; r < nr; r += 32) {
     const int p = rlag[r];
     const int s = lv - 1 - p;
     const int i0 = p < lv ? 0 : p - lv + 1;

@@ -162,6 +162,11 @@ struct Exec {
                                                 unsigned long long v) {
     return atomicCAS(p, cmp, v);
   }
+  /* sum over the lanes of the calling warp (all 32 lanes must call) */
+  RF_FN static long long warp_sum(long long v) {
+    for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+  }
   RF_FN static double dadd(double a, double b) { return __dadd_rn(a, b); }
   RF_FN static double dmul(double a, double b) { return __dmul_rn(a, b); }
   RF_FN static double ddiv(double a, double b) { return __ddiv_rn(a, b); }
@@ -249,6 +254,7 @@ struct Exec {
                                          unsigned long long v) {
     unsigned long long o = *p; if (o == cmp) *p = v; return o;
   }
+  static long long warp_sum(long long v) { return v; }
   static double dadd(double a, double b) { volatile double r = a + b; return r; }
   static double dmul(double a, double b) { volatile double r = a * b; return r; }
   static double ddiv(double a, double b) { volatile double r = a / b; return r; }
@@ -436,6 +442,7 @@ struct Arena {
   char *store_db;      /* store_cap * L */
   int32_t *nlist;      /* nlist_cap: node lists of stored structures */
   int32_t *ncnt;       /* nlist_cap: candidates of that node passing for the owning structure */
+  int32_t *ncoff;      /* nlist_cap: first candidate record of that node (copy of NodeRec::cand_off) */
   SeenEnt *seen;       /* seen_cap; lo == 0 marks an empty slot (kept clean between runs) */
   int32_t *seen_used;  /* seen_cap: occupied slots, for the clean-up */
   unsigned long long *nht;     /* nht_cap: (hash32 << 32) | (node id + 1), 0 = empty */
@@ -545,6 +552,7 @@ RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &
   RF_CARVE(store_db, char, (size_t)c.store_cap * (size_t)((L + 15) & ~15)); /* rows padded to 16 bytes */
   RF_CARVE(nlist, int32_t, c.nlist_cap);
   RF_CARVE(ncnt, int32_t, c.nlist_cap);
+  RF_CARVE(ncoff, int32_t, c.nlist_cap);
   RF_CARVE(seen_used, int32_t, c.seen_cap);
   RF_CARVE(fresh, NewRec, c.new_cap);
   RF_CARVE(sel, int32_t, fp.max_stack);
@@ -563,7 +571,7 @@ RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &
 }
 /* Byte offsets of the arena pieces (computed once on the host, bound per block/warp). */
 struct ArenaOff {
-  uint32_t seen, nht, code, node, pool16, cand, store, store_db, nlist, ncnt, seen_used, fresh, sel, sel_idx, sel_store, beam, traj_n, traj, todo, todo_id, flag, pref, sel_e;
+  uint32_t seen, nht, code, node, pool16, cand, store, store_db, nlist, ncnt, ncoff, seen_used, fresh, sel, sel_idx, sel_store, beam, traj_n, traj, todo, todo_id, flag, pref, sel_e;
 };
 RF_HD void arena_bind(Arena &A, char *base, const ArenaOff &o) {
   A.seen = (SeenEnt *)(base + o.seen);
@@ -576,6 +584,7 @@ RF_HD void arena_bind(Arena &A, char *base, const ArenaOff &o) {
   A.store_db = (char *)(base + o.store_db);
   A.nlist = (int32_t *)(base + o.nlist);
   A.ncnt = (int32_t *)(base + o.ncnt);
+  A.ncoff = (int32_t *)(base + o.ncoff);
   A.seen_used = (int32_t *)(base + o.seen_used);
   A.fresh = (NewRec *)(base + o.fresh);
   A.sel = (int32_t *)(base + o.sel);
@@ -605,6 +614,7 @@ inline void arena_offsets(ArenaOff &o, const Caps &c, const FoldParams &fp) {
   o.store_db = (uint32_t)((char *)A.store_db - base);
   o.nlist = (uint32_t)((char *)A.nlist - base);
   o.ncnt = (uint32_t)((char *)A.ncnt - base);
+  o.ncoff = (uint32_t)((char *)A.ncoff - base);
   o.seen_used = (uint32_t)((char *)A.seen_used - base);
   o.fresh = (uint32_t)((char *)A.fresh - base);
   o.sel = (uint32_t)((char *)A.sel - base);
@@ -731,6 +741,11 @@ struct Fold {
 #define fail(code) fail_at(code, __LINE__)
   RF_FN void count(int which, long long v) {
     Exec::atomic_add64(&sh->cnt[which], (unsigned long long)v);
+  }
+  /* the same for a per-thread partial sum: one atomic per warp (every thread of the block calls) */
+  RF_FN void count_all(int which, long long v) {
+    v = Exec::warp_sum(v);
+    if (Exec::lane() == 0 && v) count(which, v);
   }
 
   /* --- node creation --------------------------------------------------------------------
@@ -1068,11 +1083,18 @@ struct Fold {
   RF_FN void combo_eval(const StoreRec &S, uint64_t combo, int &e, uint64_t &lo, uint64_t &hi) const {
     e = S.e; lo = S.fp_lo; hi = S.fp_hi;
     for (int k = S.nl_n - 1; k >= 0; k--) {
-      uint32_t c = (uint32_t)A.ncnt[S.nl_off + k];
+      const uint32_t c = (uint32_t)A.ncnt[S.nl_off + k];
       if (c == 0) continue;
-      uint32_t dgt = c == 1 ? 0u : (uint32_t)(combo % c);
-      if (c != 1) combo /= c;
-      const Cand &cd = A.cand[A.node[A.nlist[S.nl_off + k]].cand_off + dgt];
+      uint32_t dgt = 0;
+      if (c != 1) {
+        if ((combo >> 32) == 0) { /* the usual case: 32-bit division */
+          const uint32_t c32 = (uint32_t)combo, q = c32 / c;
+          dgt = c32 - q * c; combo = q;
+        } else {
+          dgt = (uint32_t)(combo % c); combo /= c;
+        }
+      }
+      const Cand &cd = A.cand[A.ncoff[S.nl_off + k] + dgt];
       e += cd.dE; lo += cd.fp_lo; hi += cd.fp_hi;
     }
     if (lo == 0) lo = 1; /* 0 marks an empty slot of the seen table */
@@ -1256,6 +1278,7 @@ struct Fold {
     /* P2a: per beam member, how many stems of each of its regions pass (rafft.py:102), the size
      *      of its product, and the reference's work counters (create_childs runs for every
      *      region of every beam member) */
+    long long t_exp = 0, t_pos = 0, t_corr = 0, t_scan = 0, t_eval = 0;
     RF_PAR_BEGIN(b, beam_n)
       StoreRec &S = A.store[A.beam[b]];
       long long c_pos = 0, c_corr = 0, c_scan = 0, c_eval = 0;
@@ -1267,14 +1290,14 @@ struct Fold {
         if (!S.done) {
           int c = count_pass(nd, S.e);
           A.ncnt[S.nl_off + k] = c;
+          A.ncoff[S.nl_off + k] = nd.cand_off;
           if (c > 0) {
             mact++;
             prod = prod > (1ULL << 62) / (uint64_t)c ? (1ULL << 62) : prod * (uint64_t)c;
           }
         }
       }
-      count(CNT_NODE_EXP, S.nl_n); count(CNT_NODE_POS, c_pos); count(CNT_W_CORR, c_corr);
-      count(CNT_W_SCAN, c_scan); count(CNT_N_EVAL, c_eval); count(CNT_N_EVAL_EXPAND, c_eval);
+      t_exp += S.nl_n; t_pos += c_pos; t_corr += c_corr; t_scan += c_scan; t_eval += c_eval;
       if (!S.done) {
         S.nact = mact;
         S.prod = mact ? prod : 0;
@@ -1283,6 +1306,8 @@ struct Fold {
       cs.mprod[b] = S.done ? 0 : S.prod;
       cs.dprod[b] = S.done ? S.prod : 0;
     RF_PAR_END
+    count_all(CNT_NODE_EXP, t_exp); count_all(CNT_NODE_POS, t_pos); count_all(CNT_W_CORR, t_corr);
+    count_all(CNT_W_SCAN, t_scan); count_all(CNT_N_EVAL, t_eval); count_all(CNT_N_EVAL_EXPAND, t_eval);
     /* the members still to enumerate ("open"), in beam order, and the running sum of their
      * product sizes: the enumeration below runs over this flattened index space */
     const uint64_t SAT = 1ULL << 62;
@@ -1603,24 +1628,36 @@ struct Fold {
       if (A.todo[3 * a + 2]) cd.outer_id = id; else cd.inner_id = id;
     RF_PAR_END
     if (sh->status != ST_OK) { finish_fold(); return; }
-    /* 4d. store records + node lists (in_side then out_side per stem, rafft.py:187-190) */
-    RF_SINGLE_BEGIN
+    /* 4d. store records + node lists (in_side then out_side per stem, rafft.py:187-190): every
+     *     selected child finds its store index and the start of its node list by counting the
+     *     new children ranked before it */
+    RF_PAR_BEGIN(r, keep)
       int at = sh->n_store, nl = sh->n_nlist;
-      for (int r = 0; r < keep; r++) {
-        int i = A.sel[r];
-        if (i >= n_new) continue;
-        const NewRec &nr = A.fresh[i];
-        int cnt_nodes = A.sel_store[r];
-        StoreRec &C = A.store[at];
-        C.e = nr.e; C.fp_lo = nr.fp_lo; C.fp_hi = nr.fp_hi; C.done = 0; C.prod = 0; C.nact = 0;
-        C.nl_off = nl; C.nl_n = cnt_nodes;
-        nl += cnt_nodes;
-        A.sel_store[r] = at; /* selected rank -> store index */
-        at++;
+      for (int q = 0; q < r; q++)
+        if (A.sel[q] < n_new) { at++; nl += A.sel_store[q]; }
+      A.sel_idx[r] = at; A.pref[r] = nl;
+      if (r == keep - 1) {
+        if (A.sel[r] < n_new) { at++; nl += A.sel_store[r]; }
+        sh->tmp0 = at; sh->tmp1 = nl;
       }
-      if (nl > caps.nlist_cap) fail(ST_ERR_CAPACITY);
-      else { sh->n_nlist = nl; sh->n_store = at; }
+    RF_PAR_END
+    RF_SINGLE_BEGIN
+      if (keep > 0) {
+        if (sh->tmp1 > caps.nlist_cap) fail(ST_ERR_CAPACITY);
+        else { sh->n_nlist = sh->tmp1; sh->n_store = sh->tmp0; }
+      }
     RF_SINGLE_END
+    if (sh->status != ST_OK) { finish_fold(); return; }
+    RF_PAR_BEGIN(r, keep)
+      const int i = A.sel[r];
+      if (i < n_new) {
+        const NewRec &nr = A.fresh[i];
+        StoreRec &C = A.store[A.sel_idx[r]];
+        C.e = nr.e; C.fp_lo = nr.fp_lo; C.fp_hi = nr.fp_hi; C.done = 0; C.prod = 0; C.nact = 0;
+        C.nl_off = A.pref[r]; C.nl_n = A.sel_store[r];
+        A.sel_store[r] = A.sel_idx[r]; /* selected rank -> store index */
+      }
+    RF_PAR_END
     if (sh->status != ST_OK) { finish_fold(); return; }
     /* copy the parent's dot-bracket: one warp per row, 16 bytes per lane */
     Exec::sync();
@@ -1663,12 +1700,14 @@ struct Fold {
       }
     RF_PAR_END
     /* the next beam */
+    RF_PAR_BEGIN(r, keep)
+      const int i = A.sel[r];
+      A.sel[r] = i < n_new ? A.sel_store[r] : A.beam[i - n_new];
+    RF_PAR_END
+    RF_PAR_BEGIN(r, keep)
+      A.beam[r] = A.sel[r];
+    RF_PAR_END
     RF_SINGLE_BEGIN
-      for (int r = 0; r < keep; r++) {
-        int i = A.sel[r];
-        A.sel[r] = i < n_new ? A.sel_store[r] : A.beam[i - n_new];
-      }
-      for (int r = 0; r < keep; r++) A.beam[r] = A.sel[r];
       sh->beam_n = keep;
       sh->stage = 0;
     RF_SINGLE_END
