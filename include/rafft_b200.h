@@ -153,6 +153,12 @@ int rafft_eval_structures(rafft_ctx *ctx, const char *seqs, const char *structs,
 int rafft_kin_graph(rafft_ctx *ctx, const char *db, int32_t L, const int64_t *step_off, int32_t n_steps,
                     int32_t *uniq, uint8_t *conn, int64_t conn_cap, int64_t *conn_off);
 
+/* Landscape distance matrix (reference utility/surface.py:19-26 get_distance_matrix, which calls
+ * RNA.bp_distance for every pair): db = n dot-bracket rows of L characters; dist = n * n int32,
+ * dist[a * n + b] = number of base pairs present in exactly one of the structures a and b
+ * (symmetric, zero diagonal).  Errors as rafft_kin_graph. */
+int rafft_bp_distance_matrix(rafft_ctx *ctx, const char *db, int32_t n, int32_t L, int32_t *dist);
+
 /* Library/build identification, e.g. "rafft_b200 0.1 sm_100a". */
 const char *rafft_version(void);
 

@@ -18,7 +18,7 @@ CNT_N = len(COUNTER_NAMES)
 # every symbol include/rafft_b200.h declares (tests check the library exports all of them)
 EXPORTS = ("rafft_version", "rafft_default_energy_params", "rafft_create", "rafft_destroy",
            "rafft_last_error", "rafft_fold_batch", "rafft_fold_batch_device", "rafft_result_free",
-           "rafft_eval_structures", "rafft_kin_graph")
+           "rafft_eval_structures", "rafft_kin_graph", "rafft_bp_distance_matrix")
 
 
 class EnergyParams(C.Structure):
@@ -109,6 +109,8 @@ def lib():
     L.rafft_kin_graph.argtypes = [C.c_void_p, C.c_char_p, C.c_int32, C.POINTER(C.c_int64), C.c_int32,
                                   C.POINTER(C.c_int32), C.POINTER(C.c_uint8), C.c_int64, C.POINTER(C.c_int64)]
     L.rafft_kin_graph.restype = C.c_int
+    L.rafft_bp_distance_matrix.argtypes = [C.c_void_p, C.c_char_p, C.c_int32, C.c_int32, C.POINTER(C.c_int32)]
+    L.rafft_bp_distance_matrix.restype = C.c_int
     _lib = L
     return L
 

@@ -16,10 +16,11 @@ namespace rafft {
 
 /* one warp per structure: lane 0 parses the brackets with the two stacks of paired_positions
  * (reference rafft/utils.py:53-67: "(", "<" / ")", ">" regular, "[" / "]" pseudo-knot pile);
- * the lanes then hash the row.  bad[s] = 1 for an unbalanced or foreign character. */
+ * the lanes then hash the row.  bad[s] = 1 for a closing bracket without partner.  round_only:
+ * the ViennaRNA pair table of the distance matrix below (other brackets stay unpaired). */
 __global__ void kin_pairtable_kernel(const char *__restrict__ db, int n, int L, int16_t *__restrict__ pt,
                                      int16_t *__restrict__ stack /* n * 2 * L */, uint64_t *__restrict__ hash,
-                                     int32_t *__restrict__ bad) {
+                                     int32_t *__restrict__ bad, int round_only = 0) {
   const int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (s >= n) return;
   const char *row = db + (size_t)s * L;
@@ -28,7 +29,8 @@ __global__ void kin_pairtable_kernel(const char *__restrict__ db, int n, int L, 
     int16_t *reg = stack + (size_t)s * 2 * L, *pk = reg + L;
     int nr = 0, nk = 0, err = 0;
     for (int i = 0; i < L; i++) {
-      const char c = row[i];
+      char c = row[i];
+      if (round_only && c != '(' && c != ')') c = '.'; /* vrna_ptable: only round brackets pair */
       p[i] = -1;
       if (c == '(' || c == '<') reg[nr++] = (int16_t)i;
       else if (c == '[') pk[nk++] = (int16_t)i;
@@ -102,6 +104,59 @@ __global__ void kin_connect_kernel(const int16_t *__restrict__ pt, const int64_t
   }
   viol = __any_sync(0xffffffffu, viol);
   if (lane == 0) conn[w] = viol ? 0 : 1;
+}
+
+/* Landscape distance matrix (reference utility/surface.py:19-26, get_distance_matrix): dist[a][b] =
+ * RNA.bp_distance = number of pairs present in exactly one of the two structures, i.e. over the
+ * pair tables  sum_i [pa[i] != pb[i]] * ([pa[i] > i] + [pb[i] > i]).
+ * One block per 32 x 32 tile of the upper triangle; the 64 pair-table rows of the tile stream
+ * through shared memory in chunks of KIN_DCHUNK positions (read once per tile instead of once per
+ * pair); each of the 256 threads owns 4 pairs (one row a, four columns b).  Rows of the chunk are
+ * padded by one 32-bit word so the per-thread row walks hit distinct banks. */
+#define KIN_DTILE 32
+#define KIN_DCHUNK 128
+__global__ void __launch_bounds__(256) kin_bpdist_kernel(const int16_t *__restrict__ pt, int n, int L,
+                                                         int32_t *__restrict__ dist) {
+  /* tile (ta, tb), tb >= ta, from the linear block index */
+  const int nt = (n + KIN_DTILE - 1) / KIN_DTILE;
+  int ta = 0, rem = blockIdx.x;
+  while (rem >= nt - ta) { rem -= nt - ta; ta++; }
+  const int tb = ta + rem;
+  constexpr int ROW = KIN_DCHUNK + 2;
+  __shared__ int16_t sa[KIN_DTILE][ROW], sb[KIN_DTILE][ROW];
+  const int tid = threadIdx.x;
+  const int ra = tid >> 3, cb = (tid & 7) * 4; /* row of the a tile, first of 4 columns of the b tile */
+  int acc[4] = {0, 0, 0, 0};
+  for (int c0 = 0; c0 < L; c0 += KIN_DCHUNK) {
+    const int cl = min(KIN_DCHUNK, L - c0);
+    for (int x = tid; x < KIN_DTILE * KIN_DCHUNK; x += 256) {
+      const int r = x / KIN_DCHUNK, c = x % KIN_DCHUNK;
+      const int ga = ta * KIN_DTILE + r, gb = tb * KIN_DTILE + r;
+      sa[r][c] = (c < cl && ga < n) ? pt[(size_t)ga * L + c0 + c] : (int16_t)-1;
+      sb[r][c] = (c < cl && gb < n) ? pt[(size_t)gb * L + c0 + c] : (int16_t)-1;
+    }
+    __syncthreads();
+    for (int c = 0; c < cl; c++) {
+      const int i = c0 + c;
+      const int pa = sa[ra][c];
+      const int ua = pa > i;
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const int pb = sb[cb + k][c];
+        acc[k] += (pa != pb) ? ua + (pb > i) : 0;
+      }
+    }
+    __syncthreads();
+  }
+  const int a = ta * KIN_DTILE + ra;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const int b = tb * KIN_DTILE + cb + k;
+    if (a < n && b < n) {
+      dist[(size_t)a * n + b] = acc[k];
+      dist[(size_t)b * n + a] = acc[k];
+    }
+  }
 }
 
 }  // namespace rafft

@@ -2,7 +2,6 @@
  * rafft_cuda.cu -- the C-ABI library (include/rafft_b200.h) over the sm_100a kernels.
  *
  * Kernels in this file:
- *   order_kernel   longest-first processing order of the batch (rank by counting)
  *   fold_kernel    persistent thread blocks; each block pulls the next sequence from a device
  *                  queue and runs the whole fold (fold_core.cuh) out of its own arena
  *   scan_kernel    exclusive scans that turn per-sequence counts into the ordered layout
@@ -29,23 +28,6 @@ using namespace rafft;
 
 /* ------------------------------------------------------------------------------------ */
 /* kernels                                                                               */
-
-/* order[r] = index of the sequence with the r-th largest length (ties: lower index first);
- * subset == nullptr: all n sequences, else the n listed ones. */
-__global__ void order_kernel(const int64_t *__restrict__ offs, const int32_t *__restrict__ subset,
-                             int n, int32_t *__restrict__ order) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  int si = subset ? subset[i] : i;
-  int64_t li = offs[si + 1] - offs[si];
-  int r = 0;
-  for (int k = 0; k < n; k++) {
-    int sk = subset ? subset[k] : k;
-    int64_t lk = offs[sk + 1] - offs[sk];
-    r += (lk > li) || (lk == li && k < i);
-  }
-  order[r] = si;
-}
 
 /* Everything the phase kernels of one wave need (kernel parameter, constant bank).
  * A wave = `n` sequences folded together; slot j of the wave works on sequence order[j], owns
@@ -646,10 +628,9 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
   idx_layout(O, (char *)ctx->idx.p, n);
   if (cudaMemsetAsync(ctx->idx.p, 0, idx_bytes, ctx->stream) != cudaSuccess) { ctx->err = "memset"; return fail(RAFFT_ERR_CUDA); }
   if (int rc = dev_reserve(ctx, ctx->order, sizeof(int32_t) * (size_t)(n + 1))) return fail(rc);
-  if (int rc = dev_reserve(ctx, ctx->subset, sizeof(int32_t) * (size_t)(n + 1))) return fail(rc);
 
   std::vector<int32_t> todo;          /* sequences still to fold (empty = all) */
-  std::vector<int32_t> h_status(n > 0 ? n : 1);
+  std::vector<int32_t> h_status(n > 0 ? n : 1), h_order;
   int scale = 1;
   int64_t used[4] = {0, 0, 0, 0};      /* cursors after the previous round */
   for (int round = 0; n > 0; round++) {
@@ -688,13 +669,6 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
       ctx->big = nb;
     }
     O = N;
-    /* queue of this retry round: the m sequences, longest first */
-    const int32_t *d_subset = nullptr;
-    if (round > 0) {
-      CK(cudaMemcpyAsync(ctx->subset.p, todo.data(), sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, ctx->stream));
-      h2d_bytes += sizeof(int32_t) * (int64_t)m;
-      d_subset = (const int32_t *)ctx->subset.p;
-    }
     /* waves: as many sequences at once as the memory budget allows (one arena each) */
     size_t free_b = 0, total_b = 0;
     CK(cudaMemGetInfo(&free_b, &total_b));
@@ -752,7 +726,8 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     wc.fast_next = (int32_t *)ctx->small.p + 2 + RF_FAST_CLASSES;
     const FastShape &fsh = g_fast_shapes[ctx->fast_shape];
     const size_t fast_smem = (size_t)(fsh.threads / 32) * (size_t)fastcfg.smem_per_warp;
-    const bool any_generic = fcap == 0 || Lr > fastcfg.L_cap || Lr / 2 > fastcfg.br_cap;
+    /* a branch of a loop covers at least min_hp + 2 positions */
+    const bool any_generic = fcap == 0 || Lr > fastcfg.L_cap || Lr / (F.min_hp + 2) > fastcfg.br_cap;
     wc.out = O;
     CombineStage cs_probe;
     const size_t stage_bytes = stage_carve(cs_probe, nullptr, caps.chunk_cap, F.max_stack);
@@ -763,9 +738,24 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     }
     const int egrid = ctx->sm_count * ctx->blocks_per_sm;
     if (fcap > 0) CK(cudaFuncSetAttribute(fsh.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast_smem));
+    {
+      /* longest-first processing order (ties: input order): counting sort over the lengths on
+       * the host, which holds the offsets anyway */
+      std::vector<int32_t> start(4098, 0);
+      h_order.resize((size_t)m);
+      for (int k = 0; k < m; k++) {
+        const int si = round == 0 ? k : todo[k];
+        start[4096 - (int)(h_offs[si + 1] - h_offs[si]) + 1]++;
+      }
+      for (int b = 0; b < 4097; b++) start[b + 1] += start[b];
+      for (int k = 0; k < m; k++) {
+        const int si = round == 0 ? k : todo[k];
+        h_order[(size_t)start[4096 - (int)(h_offs[si + 1] - h_offs[si])]++] = si;
+      }
+      CK(cudaMemcpyAsync(ctx->order.p, h_order.data(), sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, ctx->stream));
+      h2d_bytes += sizeof(int32_t) * (int64_t)m;
+    }
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
-    order_kernel<<<(m + 255) / 256, 256, 0, ctx->stream>>>(d_offs, d_subset, m, (int32_t *)ctx->order.p);
-    launches++;
     for (int64_t w0 = 0; w0 < m; w0 += wave) {
       const int nw = (int)std::min<int64_t>(wave, m - w0);
       wc.order = (const int32_t *)ctx->order.p + w0;
@@ -1032,6 +1022,34 @@ int rafft_kin_graph(rafft_ctx *ctx, const char *db, int32_t L, const int64_t *st
   CK(cudaStreamSynchronize(ctx->stream));
   for (int64_t i = 0; i < n; i++)
     if (bad[(size_t)i]) { ctx->err = "rafft_kin_graph: closing bracket without partner in structure " + std::to_string(i); return RAFFT_ERR_SEQ; }
+  return RAFFT_OK;
+}
+
+int rafft_bp_distance_matrix(rafft_ctx *ctx, const char *db, int32_t n, int32_t L, int32_t *dist) {
+  if (!ctx) return RAFFT_ERR_ARG;
+  if (n < 0 || L < 1 || L > 32767 || (n > 0 && (!db || !dist))) { ctx->err = "rafft_bp_distance_matrix: bad argument"; return RAFFT_ERR_ARG; }
+  if (n == 0) return RAFFT_OK;
+  if (n > 46340) { ctx->err = "rafft_bp_distance_matrix: too many structures"; return RAFFT_ERR_ARG; }
+  CK(cudaSetDevice(ctx->device));
+  /* db | pt | stacks | hash | bad | dist */
+  size_t o_db = 0, o_pt = align_up((size_t)n * L, 256), o_st = align_up(o_pt + sizeof(int16_t) * (size_t)n * L, 256),
+         o_hash = align_up(o_st + sizeof(int16_t) * 2 * (size_t)n * L, 256), o_bad = o_hash + sizeof(uint64_t) * (size_t)n,
+         o_dist = align_up(o_bad + sizeof(int32_t) * (size_t)n, 256), o_end = o_dist + sizeof(int32_t) * (size_t)n * n;
+  if (int rc = dev_reserve(ctx, ctx->kinbuf, o_end)) return rc;
+  char *d = (char *)ctx->kinbuf.p;
+  CK(cudaMemcpyAsync(d + o_db, db, (size_t)n * L, cudaMemcpyHostToDevice, ctx->stream));
+  const int wpb = 4;
+  kin_pairtable_kernel<<<(unsigned)((n + wpb - 1) / wpb), wpb * 32, 0, ctx->stream>>>(
+      d + o_db, (int)n, L, (int16_t *)(d + o_pt), (int16_t *)(d + o_st), (uint64_t *)(d + o_hash), (int32_t *)(d + o_bad), 1);
+  const int nt = (n + KIN_DTILE - 1) / KIN_DTILE;
+  kin_bpdist_kernel<<<(unsigned)(nt * (nt + 1) / 2), 256, 0, ctx->stream>>>((const int16_t *)(d + o_pt), n, L, (int32_t *)(d + o_dist));
+  CK(cudaGetLastError());
+  std::vector<int32_t> bad((size_t)n);
+  CK(cudaMemcpyAsync(bad.data(), d + o_bad, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaMemcpyAsync(dist, d + o_dist, sizeof(int32_t) * (size_t)n * n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  for (int i = 0; i < n; i++)
+    if (bad[(size_t)i]) { ctx->err = "rafft_bp_distance_matrix: closing bracket without partner in structure " + std::to_string(i); return RAFFT_ERR_SEQ; }
   return RAFFT_OK;
 }
 

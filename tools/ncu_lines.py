@@ -6,7 +6,11 @@ import collections, csv, io, os, re, subprocess, sys, tempfile
 
 rep, lib, kern = sys.argv[1:4]
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
-src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+if rep.endswith(".gz"):  # source page already exported on the GPU box (tools/evidence.sh)
+    import gzip
+    src = gzip.open(rep, "rt").read()
+else:
+    src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
 hi = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
 H = rows[hi]
