@@ -373,6 +373,10 @@ __device__ __forceinline__ void fast_p5(RF_FAST_ARGS) {
   RF_FAST_BIND
   const double dGC = prm.w[1][2], dAU = prm.w[0][3], dGU = prm.w[2][3];
   const unsigned mGC = dGC == 0.0 ? 0u : FULL, mAU = dAU == 0.0 ? 0u : FULL, mGU = dGU == 0.0 ? 0u : FULL;
+  /* through a shuffle so that they live in registers: ptxas otherwise re-loads them from the
+   * constant bank inside the bit loop */
+  const int hGC = __shfl_sync(FULL, __double2hiint(dGC), 0), hAU = __shfl_sync(FULL, __double2hiint(dAU), 0),
+            hGU = __shfl_sync(FULL, __double2hiint(dGU), 0);
   /* Scan order: the ranked lags by decreasing length of their anti-diagonal (p = lv-1, lv-2, lv,
    * lv-3, lv+1, ...), compacted by ballot.  Every lane scans one lag per round; lanes of a
    * round then carry nearly the same work and the incomplete last round holds the shortest
@@ -403,12 +407,13 @@ __device__ __forceinline__ void fast_p5(RF_FAST_ARGS) {
     /* hairpin test (rafft.py:78): pos[j] - pos[i] decreases along the scan, so the positions
      * that fail it are the innermost ones; they can never become the stem and are clipped */
     while (iend > i0 && !((int)pos[p - (iend - 1)] - (int)pos[iend - 1] > prm.min_hp)) iend--;
-    int max_nb = 0, tmp_max = 0, max_i = 0, max_j = 0;
+    int max_i = 0, max_j = 0;
     double max_score = 0.0, prev = 0.0;
     unsigned carry = 0; /* was the position just before this word pairable (and in range)? */
     unsigned best_bit = 0;
-    int best_wi = 0;
-    for (int wi = i0 >> 5; wi <= ((iend - 1) >> 5) && iend > i0; wi++) {
+    /* run length so far in the low half, word index in the high half: one register to keep */
+    int run_w = (i0 >> 5) << 16, best_rw = 0;
+    for (int wi = i0 >> 5; wi <= ((iend - 1) >> 5) && iend > i0; wi++, run_w += 0x10000) {
       const unsigned fh = FH[wi], fl = FL[wi];
       const unsigned x = fh ^ fast_shift(RH, wi, s), y = fl ^ fast_shift(RL, wi, s);
       unsigned range = FULL;
@@ -422,19 +427,22 @@ __device__ __forceinline__ void fast_p5(RF_FAST_ARGS) {
       /* both arms continue in original coordinates (rafft.py:67), t > 0 */
       unsigned IS = CL[wi] & fast_shift(CLR, wi, s - 1);
       if ((i0 >> 5) == wi) IS &= ~(1u << (i0 & 31));
+      const int wbase = wi << 16;
       while (Pm) {
         const unsigned bit = Pm & (0u - Pm);
         Pm ^= bit;
-        const double w = (gc & bit) ? dGC : (au & bit) ? dAU : dGU;
+        /* the weights are multiples of 1/16 up to 16: the low words of the doubles are zero */
+        const double w = __hiloint2double((gc & bit) ? hGC : (au & bit) ? hAU : hGU, 0);
         const bool adjacent = (ADJ & bit) != 0;
-        double tot = w;
-        if (IS & bit) tot = __dmul_rn(__dadd_rn(adjacent ? prev : 0.0, w), w);
-        tmp_max = adjacent ? tmp_max + 1 : 1;
-        if (tot >= max_score) { max_score = tot; max_nb = tmp_max; best_bit = bit; best_wi = wi; }
+        const double chained = __dmul_rn(__dadd_rn(adjacent ? prev : 0.0, w), w);
+        const double tot = (IS & bit) ? chained : w;
+        run_w = adjacent ? run_w + 1 : wbase + 1;
+        if (tot >= max_score) { max_score = tot; best_rw = run_w; best_bit = bit; }
         prev = tot;
       }
     }
-    if (best_bit) { max_i = 32 * best_wi + __ffs((int)best_bit) - 1; max_j = p - max_i; }
+    const int max_nb = best_rw & 0xffff;
+    if (best_bit) { max_i = 32 * (best_rw >> 16) + __ffs((int)best_bit) - 1; max_j = p - max_i; }
     w_scan += len2;
     r_stem[r] = ((uint32_t)max_i << 16) | (uint32_t)max_j;
     r_nb[r] = (uint16_t)max_nb;
