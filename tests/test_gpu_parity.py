@@ -198,6 +198,27 @@ def test_cli_reproduces_example_file():
     assert out.stdout == open(os.path.join(GOLDEN, "rafft.out")).read()
 
 
+def test_cli_batch_fasta_and_bench_line(tmp_path, oracle):
+    """wire formats: a multi-record FASTA folded as one batch; the --bench line of
+    bin/rafft:66 (`seq len struct E nbp`) and the final-structure blocks, against the oracle"""
+    from rafft_b200.synth import splitmix_seq
+    from rafft_b200.utils import energy_from_dcal
+    seqs = [splitmix_seq(700 + k, L) for k, L in enumerate((31, 64, 97, 150))]
+    fa = tmp_path / "in.fa"
+    fa.write_text("".join(">s%d some text\n%s\n%s\n" % (k, s[:40].replace("U", "T"), s[40:]) for k, s in enumerate(seqs)))
+    run = lambda *a: subprocess.run([sys.executable, os.path.join(ROOT, "bin", "rafft"), "-sf", str(fa), "--batch",
+                                     "-n", "50", "-ms", "4"] + list(a), capture_output=True, text=True, timeout=300)
+    want = [oracle.fold(s, 50, 4, 1000)[-1] for s in seqs]          # last beam: [(db, dcal)]
+    out = run("--bench")
+    assert out.returncode == 0, out.stderr
+    lines = ["%s %d %s %6.1f %d" % (s, len(s), db, energy_from_dcal(e), db.count("(")) for s, beam in zip(seqs, want) for db, e in beam]
+    assert out.stdout.splitlines() == lines
+    out = run()
+    assert out.returncode == 0, out.stderr
+    lines = [l for s, beam in zip(seqs, want) for l in [s] + ["%s %6.1f" % (db, energy_from_dcal(e)) for db, e in beam]]
+    assert out.stdout.splitlines() == lines
+
+
 def test_fold_api_like_reference(ctx):
     from rafft_b200 import fold
     seq = open(os.path.join(GOLDEN, "rafft_20.out")).readline().strip()

@@ -2,6 +2,7 @@
 # Round evidence, run on the GPU box under gpurun:  tools/evidence.sh <tag> [kernels...]
 #   1. bench.py (cfg2, default flags minus the CPU baseline) -> gpurun_out/<tag>_bench.json
 #   2. ncu launch list of a 1-step bench                     -> gpurun_out/<tag>_launches.csv
+#   2b. ncu DRAM byte counters of every launch           -> gpurun_out/<tag>_dram.csv
 #   3. one `ncu --set full` capture per kernel named (folding iteration 2, the largest, of the first
 #      fold): raw and source pages exported as CSV on the box (the .ncu-rep files together exceed
 #      the 64 MiB that travel back); only the first kernel's .ncu-rep is kept.
@@ -15,6 +16,9 @@ python bench.py --steps 5 --warmup 3 --no-cpu-baseline > $out/${tag}_bench.json 
 python bench.py --steps 1 --warmup 1 --no-cpu-baseline > /dev/null 2>&1 || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/${tag}_launches.csv \
   python bench.py --steps 1 --warmup 1 --no-cpu-baseline > $out/${tag}_ncu.log 2>&1
+# DRAM bytes of every launch (two folds: warm-up + step) -> per-kernel traffic per launch (tools/traffic_table.py)
+ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 600 --csv --log-file $out/${tag}_dram.csv \
+  python bench.py --steps 1 --warmup 1 --no-cpu-baseline > $out/${tag}_dram.log 2>&1
 first=1
 for k in $kernels; do
   rep=/tmp/${tag}_$k
