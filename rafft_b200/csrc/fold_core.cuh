@@ -471,7 +471,13 @@ struct WarpScratch {
   uint32_t *r_stem; /* nb_mode: (max_i << 16) | max_j */
   int32_t *r_nb;    /* nb_mode */
   int32_t *tmp;     /* 8 ints */
+  uint64_t *sel;    /* RF_SEL_CAP + RF_SEL_SAMPLE keys when key_cap > RF_SEL_MIN: top-n selection (expand_e2) */
 };
+
+/* Regions with more than RF_SEL_MIN (padded) lags rank by selection instead of a full sort. */
+#define RF_SEL_MIN 2048
+#define RF_SEL_CAP 2048
+#define RF_SEL_SAMPLE 256
 
 /* Per-sequence state that lives across the phase kernels (global memory; the block-scope
  * kernels work on a shared-memory copy). */
@@ -528,6 +534,7 @@ RF_HD size_t wscratch_carve(WarpScratch &W, char *base, const Caps &c, const Fol
   RF_WCARVE(r_stem, uint32_t, nrank);
   RF_WCARVE(r_nb, int32_t, nrank);
   RF_WCARVE(tmp, int32_t, 8);
+  RF_WCARVE(sel, uint64_t, c.key_cap > RF_SEL_MIN ? RF_SEL_CAP + RF_SEL_SAMPLE : 0);
 #undef RF_WCARVE
   return align_up(off, 128);
 }
@@ -908,7 +915,43 @@ struct Fold {
   }
   RF_FN void expand_e2(NodeRec &n, WarpScratch &W) {
     RF_EXPAND_VARS
-    /* 3. rank: the first nb_mode lags in (value desc, lag desc) order */
+    /* 3. rank: the first nb_mode lags in (value desc, lag desc) order.  Long regions select
+     *    instead of sorting everything: a pivot from a sorted sample of the keys is aimed at
+     *    ~3 nb_mode keys above it; those are compacted and sorted (the keys are distinct -- the
+     *    lag sits in their low bits -- so the result is the same as the full sort's).  A pivot
+     *    that leaves fewer than nb_mode or more than RF_SEL_CAP keys falls back to the full sort. */
+    if (nk > RF_SEL_MIN && caps.key_cap > RF_SEL_MIN) {
+      uint64_t *const smp = W.sel + RF_SEL_CAP;
+      const int stride = nk / RF_SEL_SAMPLE;
+      RF_WPAR_BEGIN(x, RF_SEL_SAMPLE)
+        smp[x] = W.keys[x * stride + (stride >> 1)];
+      RF_WPAR_END
+      wsort(smp, RF_SEL_SAMPLE, true);
+      const int pidx = (int)((3LL * nr * RF_SEL_SAMPLE + nlag - 1) / nlag) + 4;
+      if (pidx < RF_SEL_SAMPLE) {
+        const uint64_t pivot = smp[pidx];
+        RF_WPAR_BEGIN(x, nk)
+          const uint64_t k = W.keys[x];
+          if (k >= pivot) {
+            const int at = Exec::atomic_add(&W.tmp[4], 1);
+            if (at < RF_SEL_CAP) W.sel[at] = k;
+          }
+        RF_WPAR_END
+        const int cnt = W.tmp[4];
+        if (cnt >= nr && cnt <= RF_SEL_CAP) {
+          int np = 32;
+          while (np < cnt) np <<= 1;
+          RF_WPAR_BEGIN(x, np - cnt)
+            W.sel[cnt + x] = 0;
+          RF_WPAR_END
+          wsort(W.sel, np, true);
+          RF_WPAR_BEGIN(r, nr)
+            W.ranked[r] = (int)(W.sel[r] & 0x1FFFULL);
+          RF_WPAR_END
+          return;
+        }
+      }
+    }
     wsort(W.keys, nk, true);
     RF_WPAR_BEGIN(r, nr)
       W.ranked[r] = (int)(W.keys[r] & 0x1FFFULL);

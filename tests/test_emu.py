@@ -67,3 +67,13 @@ def test_emu_task_queue_overflow_defers(emu, oracle):
         want, wcnt = oracle.fold(seq, 50, 10, 1000, counters=True)
         assert rc == 0 and steps == want
         assert cnt[:5] == wcnt[:5]
+
+
+def test_emu_long_region_ranks_by_selection(emu, oracle):
+    """regions with more than 2048 padded lags (lv > 1024) rank by pivot selection (expand_e2):
+    same trajectory as the oracle, forward and reversed iteration order"""
+    seq = splitmix_seq(4242, 1300)
+    want = oracle.fold(seq, 60, 3, 1000)
+    for rev in (0, 1):
+        rc, steps, _, _ = emu(seq, reverse=rev, scale=4, nb_mode=60, max_stack=3)
+        assert rc == 0 and steps == want
