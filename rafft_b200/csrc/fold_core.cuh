@@ -465,7 +465,7 @@ struct WarpScratch {
   uint64_t *keys;   /* key_cap: lag keys, later candidate keys */
   uint16_t *pos;    /* L_max: local index -> original position */
   uint16_t *brcnt;  /* L_max: branches of the loop before that position */
-  uint32_t *mask;   /* 10 * mask_words: F[A,C,G,U], R[A,C,G,U] (reversed), CL, CLR */
+  uint32_t *mask;   /* 14 * mask_words: F[A,C,G,U], R[A,C,G,U] (reversed), CL, CLR, bit planes FH, FL, RH, RL */
   int32_t *ranked;  /* nb_mode: lag of rank r */
   int32_t *r_dE;    /* nb_mode */
   uint32_t *r_stem; /* nb_mode: (max_i << 16) | max_j */
@@ -528,7 +528,7 @@ RF_HD size_t wscratch_carve(WarpScratch &W, char *base, const Caps &c, const Fol
   RF_WCARVE(keys, uint64_t, c.key_cap);
   RF_WCARVE(pos, uint16_t, c.L_max);
   RF_WCARVE(brcnt, uint16_t, c.L_max);
-  RF_WCARVE(mask, uint32_t, 10 * (size_t)c.mask_words);
+  RF_WCARVE(mask, uint32_t, 14 * (size_t)c.mask_words);
   RF_WCARVE(ranked, int32_t, nrank);
   RF_WCARVE(r_dE, int32_t, nrank);
   RF_WCARVE(r_stem, uint32_t, nrank);
@@ -894,16 +894,32 @@ struct Fold {
      *    key = order-preserving bits of c[p] with the lag in the low bits, so that sorting
      *    keys descending is the reference's (value desc, lag desc) order (rafft.py:118,92). */
     const int wGC = prm.wi[1][2], wAU = prm.wi[0][3], wGU = prm.wi[2][3];
+    /* bit planes of the base codes (A,C,G,U = 0..3): with x = FH ^ RH', y = FL ^ RL' (R' shifted to
+     * the lag) the G.C pairs are x&y&(FH^FL), A.U x&y&~(FH^FL), G.U ~x&y&FH -- both orientations
+     * at once, so only the first half of the anti-diagonal is visited */
+    uint32_t *const FH = W.mask + 10 * MW, *const FL = FH + MW, *const RH = FL + MW, *const RL = RH + MW;
+    RF_WPAR_BEGIN(x, MW)
+      FH[x] = F[2 * MW + x] | F[3 * MW + x];
+      FL[x] = F[1 * MW + x] | F[3 * MW + x];
+      RH[x] = R[2 * MW + x] | R[3 * MW + x];
+      RL[x] = R[1 * MW + x] | R[3 * MW + x];
+    RF_WPAR_END
     RF_WPAR_BEGIN(p, nk)
       uint64_t key = 0;
       if (p < nlag) {
         const int s = lv - 1 - p;
-        const int i0 = p < lv ? 0 : p - lv + 1, i1 = p < lv ? p : lv - 1;
+        const int i0 = p < lv ? 0 : p - lv + 1;
+        const int d = p < lv ? p + 1 : 2 * lv - 1 - p;
+        const int iend = i0 + ((d + 1) >> 1); /* exclusive */
         int acc = 0;
-        for (int wi = i0 >> 5; wi <= (i1 >> 5); wi++) {
-          unsigned fg = F[2 * MW + wi], fa = F[0 * MW + wi];
-          unsigned rc = mshift(R + 1 * MW, wi, s, nw), ru = mshift(R + 3 * MW, wi, s, nw);
-          acc += wGC * Exec::popc(fg & rc) + wAU * Exec::popc(fa & ru) + wGU * Exec::popc(fg & ru);
+        for (int wi = i0 >> 5; wi <= ((iend - 1) >> 5); wi++) {
+          const unsigned fh = FH[wi], fl = FL[wi];
+          const unsigned x = fh ^ mshift(RH, wi, s, nw), y = fl ^ mshift(RL, wi, s, nw);
+          unsigned range = 0xffffffffu;
+          if (32 * wi < i0) range &= 0xffffffffu << (i0 - 32 * wi);
+          if (32 * wi + 32 > iend) range &= 0xffffffffu >> (32 * wi + 32 - iend);
+          const unsigned xy = x & y & range, t = fh ^ fl;
+          acc += wGC * Exec::popc(xy & t) + wAU * Exec::popc(xy & ~t) + wGU * Exec::popc(~x & y & fh & range);
         }
         double cor = Exec::ddiv((double)(2 * (int64_t)acc), 16.0);
         double norm = (double)(p < lv ? p : 2 * lv - 2 - p) + 1.0;
