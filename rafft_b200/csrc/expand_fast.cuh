@@ -35,7 +35,7 @@ struct FastCfg {
   int32_t mws;     /* words per mask incl. one zero word on either side: L_cap/32 + 2 */
   int32_t wgc, wau, wgu; /* pair weights divided by their gcd (small integers) */
   int32_t smem_per_warp;
-  int32_t o_mask, o_pos, o_brcnt, o_lcode, o_pre, o_rlag, o_A; /* byte offsets in the warp slice */
+  int32_t o_mask, o_pos, o_brcnt, o_lcode, o_pre, o_A; /* byte offsets in the warp slice */
   int32_t o_stem, o_ck, o_nb;                                  /* pieces of A after the ranking */
   int32_t o_wst;                                               /* 4 ints of warp state */
   int32_t o_rank; /* rank of every lag (uint16), behind o_nb inside A; dead once the scan order is built */
@@ -66,7 +66,6 @@ inline bool build_fast_cfg(FastCfg &fc, int L_max, const FoldParams &F) {
   fc.o_brcnt = carve((size_t)fc.L_cap);
   fc.o_lcode = carve((size_t)fc.L_cap);
   fc.o_pre = carve(4 * 2 * (size_t)(fc.br_cap + 1));
-  fc.o_rlag = carve(2 * (size_t)nr);
   fc.o_wst = carve(16);
   size_t a_keys = 4 * (size_t)nk_cap;
   size_t a_after = 4 * (size_t)nr + 4 * (size_t)ck_cap + 2 * (size_t)nr + 32 + 2 * (size_t)nk_cap;
@@ -239,7 +238,6 @@ __device__ __forceinline__ int fast_stem_dE(const FastTask &T, const EnergyView 
   uint8_t *brcnt = (uint8_t *)(ws + fc.o_brcnt);                                                \
   uint8_t *lcode = (uint8_t *)(ws + fc.o_lcode);                                                \
   int32_t *pre_ml = (int32_t *)(ws + fc.o_pre), *pre_ext = pre_ml + (fc.br_cap + 1);            \
-  uint16_t *rlag = (uint16_t *)(ws + fc.o_rlag);                                                \
   uint32_t *keys = (uint32_t *)(ws + fc.o_A);                                                   \
   uint32_t *r_stem = (uint32_t *)(ws + fc.o_stem);                                              \
   uint32_t *ck = (uint32_t *)(ws + fc.o_ck);                                                    \
@@ -249,7 +247,7 @@ __device__ __forceinline__ int fast_stem_dE(const FastTask &T, const EnergyView 
   const int nr = nlag < prm.nb_mode ? nlag : prm.nb_mode;                                       \
   const unsigned FULL = 0xffffffffu;                                                            \
   (void)code; (void)br; (void)ci; (void)cj; (void)m; (void)FH; (void)FL; (void)RH; (void)RL; (void)CL; (void)CLR;     \
-  (void)pos; (void)brcnt; (void)lcode; (void)pre_ml; (void)pre_ext; (void)rlag; (void)keys;     \
+  (void)pos; (void)brcnt; (void)lcode; (void)pre_ml; (void)pre_ext; (void)keys;     \
   (void)r_stem; (void)ck; (void)r_nb; (void)wst; (void)nr; (void)FULL;
 
 #define RF_FAST_ARGS                                                                            \

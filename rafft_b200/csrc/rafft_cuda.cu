@@ -386,7 +386,7 @@ struct rafft_ctx {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, evx0 = nullptr, evx1 = nullptr;
   DevEnergy *d_energy = nullptr;
-  DevBuf arenas, seqs, offs, order, subset, idx, big, ordered, scan, evalbuf, states, tasks, ftasks, scratch, small, kinbuf;
+  DevBuf arenas, seqs, offs, order, idx, big, ordered, scan, evalbuf, states, tasks, ftasks, scratch, small, kinbuf;
   std::vector<HostBlock> pinned_free;
   int64_t *h_small = nullptr; /* pinned: totals + cursors */
   int block_threads = 64;   /* threads per block of the block-scope phase kernels */
@@ -471,7 +471,7 @@ const char *rafft_last_error(const rafft_ctx *ctx) { return ctx ? ctx->err.c_str
 void rafft_destroy(rafft_ctx *ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
-  DevBuf *bufs[] = {&ctx->arenas, &ctx->seqs, &ctx->offs, &ctx->order, &ctx->subset, &ctx->idx,
+  DevBuf *bufs[] = {&ctx->arenas, &ctx->seqs, &ctx->offs, &ctx->order, &ctx->idx,
                     &ctx->states, &ctx->tasks, &ctx->ftasks, &ctx->scratch, &ctx->small,
                     &ctx->big, &ctx->ordered, &ctx->scan, &ctx->evalbuf, &ctx->kinbuf};
   for (DevBuf *b : bufs)
