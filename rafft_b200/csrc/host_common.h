@@ -154,10 +154,15 @@ inline Caps make_caps(int L_max, const FoldParams &F, int nthreads, int scale) {
   c.pool16_cap = c.node_cap * 12;
   int per_node = F.nb_mode / 4 < 8 ? 8 : F.nb_mode / 4 > 64 ? 64 : F.nb_mode / 4;
   c.cand_cap = (int32_t)(node_base * per_node);
-  c.store_cap = (int32_t)(1 + ms * 12 * scale);
-  c.nlist_cap = c.store_cap * 12;
+  /* structures that ever enter a beam, and their region lists: both grow with the number of
+   * folding steps, i.e. with the length (3000 nt, -ms 200: 3.5k structures, 18 regions each) */
+  const int64_t per_ms = 16 > c.L_max / 64 ? 16 : c.L_max / 64, per_st = 12 > c.L_max / 100 ? 12 : c.L_max / 100;
+  c.store_cap = (int32_t)(1 + (ms * per_ms + 48) * scale); /* at least one per folding step (-ms 1) */
+  c.nlist_cap = (int32_t)(c.store_cap * per_st);
   c.new_cap = (int32_t)(mbc + ms + 1);
-  c.seen_cap = pow2_at_least(16 * (mbc + ms) * scale + 64);
+  /* up to max_branch + max_stack new fingerprints per folding step, table kept under half full;
+   * the number of steps grows with the length (13 at <= 500 nt, 20-35 at 3000-4000 nt) */
+  c.seen_cap = pow2_at_least((16 + c.L_max / 50) * (mbc + ms) * scale + 64);
   c.nht_cap = pow2_at_least(4 * (int64_t)c.node_cap);
   c.step_cap = 48 * scale;
   c.todo_cap = (int32_t)(256 + 8 * ms) * scale;

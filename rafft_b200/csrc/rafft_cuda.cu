@@ -799,6 +799,19 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
       }
       k_finish<<<nw, RF_BLOCK_THREADS_MAX, 0, ctx->stream>>>(wc);
       launches++;
+      if (dbg) { /* high-water marks of the arena pieces against their capacities */
+        std::vector<SeqState> hs((size_t)nw);
+        cudaMemcpyAsync(hs.data(), ctx->states.p, sizeof(SeqState) * (size_t)nw, cudaMemcpyDeviceToHost, ctx->stream);
+        cudaStreamSynchronize(ctx->stream);
+        int hw[7] = {0, 0, 0, 0, 0, 0, 0};
+        for (const SeqState &q : hs) {
+          const int v[7] = {q.n_node, q.n_pool16, q.n_cand, q.n_store, q.n_nlist, q.n_seen, q.n_steps};
+          for (int k = 0; k < 7; k++) hw[k] = std::max(hw[k], v[k]);
+        }
+        fprintf(stderr, "[rafft] high water (cap): node %d (%d) pool16 %d (%d) cand %d (%d) store %d (%d) nlist %d (%d) seen %d (%d) steps %d (%d); arena %.1f MB, scale %d\n",
+                hw[0], caps.node_cap, hw[1], caps.pool16_cap, hw[2], caps.cand_cap, hw[3], caps.store_cap, hw[4], caps.nlist_cap,
+                hw[5], caps.seen_cap, hw[6], caps.step_cap, caps.arena_bytes / 1048576.0, scale);
+      }
     }
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
     CK(cudaGetLastError());

@@ -89,6 +89,7 @@ int emu_fold(const rafft_energy_params *ep_in, const char *seq, int L, const raf
     for (size_t k = 0; k < tb; k++)
       if (arena[k]) { fprintf(stderr, "emu_fold: hash tables not clean after run\n"); return -2; }
   }
+  if (status[0] == ST_ERR_CAPACITY && getenv("EMU_VERBOSE")) fprintf(stderr, "emu_fold: capacity exceeded at fold_core.cuh line %d\n", -sh.fail_line < 0 ? sh.fail_line : -sh.fail_line);
   if (cnt) for (int k = 0; k < CNT_N; k++) cnt[k] = counters[k];
   if (hiwater) {
     hiwater[0] = sh.n_node; hiwater[1] = sh.n_pool16; hiwater[2] = sh.n_cand; hiwater[3] = sh.n_store;

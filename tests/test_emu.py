@@ -75,5 +75,5 @@ def test_emu_long_region_ranks_by_selection(emu, oracle):
     seq = splitmix_seq(4242, 1300)
     want = oracle.fold(seq, 60, 3, 1000)
     for rev in (0, 1):
-        rc, steps, _, _ = emu(seq, reverse=rev, scale=4, nb_mode=60, max_stack=3)
+        rc, steps, _, _ = emu(seq, reverse=rev, nb_mode=60, max_stack=3)
         assert rc == 0 and steps == want
