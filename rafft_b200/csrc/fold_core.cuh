@@ -491,7 +491,7 @@ struct SeqState {
   int32_t tmp0, tmp1, tmp2, cur_b, xcut;
   int32_t fail_line;       /* source line of the first capacity failure (diagnostics) */
   int32_t exp_from;        /* loop records from this id on may still need their expansion */
-  int32_t qcnt[8], qbase[8]; /* gather: regions per work list (6 size classes + generic) */
+  int32_t qcnt[16], qbase[16]; /* gather: regions per work list (RF_FAST_LISTS fast lists + generic) */
   int32_t emin, emax, cnt_le;
   int32_t wsum[12];
   int64_t seq_off;         /* first letter of the sequence in the batch text */
@@ -501,6 +501,9 @@ typedef SeqState BlockShared;
 
 /* Region-expansion work list of one round: (sequence slot, node id) + one scratch slot each. */
 #define RF_FAST_CLASSES 6
+/* every size class (32 << class padded lags) has two work lists, lower and upper half of its lag
+ * range: the regions a block expands together are then within 1.5x of each other */
+#define RF_FAST_LISTS (2 * RF_FAST_CLASSES)
 struct TaskQueue {
   int32_t *n_tasks;   /* device counter; may overshoot cap */
   int32_t cap;
@@ -509,9 +512,9 @@ struct TaskQueue {
   int32_t self;       /* slot of the sequence this Fold works on (block scope) */
   /* second list: regions small enough for the shared-memory expansion (expand_fast.cuh);
    * fast_cap == 0 (host emulation) sends everything to the first list */
-  int32_t *n_fast;    /* RF_FAST_CLASSES counters: one list per size class (32 << class lags) */
+  int32_t *n_fast;    /* RF_FAST_LISTS counters */
   int32_t fast_cap, fast_lv, fast_br;
-  int32_t *fast_task; /* RF_FAST_CLASSES lists of fast_cap tasks, 2 ints per task */
+  int32_t *fast_task; /* RF_FAST_LISTS lists of fast_cap tasks, 2 ints per task */
 };
 
 RF_HD size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
@@ -1283,7 +1286,7 @@ struct Fold {
         sh->stage = 1;
       }
       sh->expand_pending = 0;
-      for (int c = 0; c < 8; c++) sh->qcnt[c] = 0;
+      for (int c = 0; c < 16; c++) sh->qcnt[c] = 0;
     RF_SINGLE_END
     if (sh->status != ST_OK) { finish_fold(); return; }
     /* P1: the loops that have not been expanded yet become warp tasks.  They are exactly the loop
@@ -1292,10 +1295,11 @@ struct Fold {
      * and block instead of one atomic per region. */
     const int from = sh->exp_from, n_new_nodes = sh->n_node - from;
 #define RF_GATHER_CLASS(nd, cls)                                                              \
-  int cls = RF_FAST_CLASSES;                                                                  \
+  int cls = RF_FAST_LISTS;                                                                    \
   if (Q.fast_cap > 0 && (nd).lv <= Q.fast_lv && (nd).br_n <= Q.fast_br) {                     \
-    cls = 0;                                                                                  \
-    while ((32 << cls) < 2 * (nd).lv - 1) cls++;                                              \
+    int k2 = 0;                                                                               \
+    while ((32 << k2) < 2 * (nd).lv - 1) k2++;                                                \
+    cls = 2 * k2 + (2 * (nd).lv - 1 > (24 << k2) ? 1 : 0);                                    \
   }
     RF_PAR_BEGIN(x, n_new_nodes)
       const NodeRec &nd = A.node[from + x];
@@ -1305,8 +1309,8 @@ struct Fold {
       }
     RF_PAR_END
     RF_SINGLE_BEGIN
-      for (int c = 0; c <= RF_FAST_CLASSES; c++) {
-        if (sh->qcnt[c]) sh->qbase[c] = Exec::atomic_add(c < RF_FAST_CLASSES ? Q.n_fast + c : Q.n_tasks, sh->qcnt[c]);
+      for (int c = 0; c <= RF_FAST_LISTS; c++) {
+        if (sh->qcnt[c]) sh->qbase[c] = Exec::atomic_add(c < RF_FAST_LISTS ? Q.n_fast + c : Q.n_tasks, sh->qcnt[c]);
         sh->qcnt[c] = 0;
       }
     RF_SINGLE_END
@@ -1314,7 +1318,7 @@ struct Fold {
       NodeRec &nd = A.node[from + x];
       if (nd.nht_slot >= 0 && nd.cand_n == -1) {
         RF_GATHER_CLASS(nd, cls)
-        const bool fast = cls < RF_FAST_CLASSES;
+        const bool fast = cls < RF_FAST_LISTS;
         int32_t *list = fast ? Q.fast_task + 2 * (size_t)cls * (size_t)Q.fast_cap : Q.task;
         const int cap = fast ? Q.fast_cap : Q.cap;
         const int at = sh->qbase[cls] + Exec::atomic_add(&sh->qcnt[cls], 1);

@@ -207,12 +207,18 @@ __global__ void __launch_bounds__(THREADS, MINB) k_expand_fast(RF_WAVE_PARAM) {
   __shared__ int s_base;
   char *ws = fast_smem + (size_t)(threadIdx.x >> 5) * (size_t)c.fast.smem_per_warp;
   /* largest regions first */
-  fast_class<32>(c, 5, ws, &s_base);
-  fast_class<16>(c, 4, ws, &s_base);
-  fast_class<8>(c, 3, ws, &s_base);
-  fast_class<4>(c, 2, ws, &s_base);
-  fast_class<2>(c, 1, ws, &s_base);
-  fast_class<1>(c, 0, ws, &s_base);
+#pragma unroll 1
+  for (int sub = 1; sub >= 0; sub--) fast_class<32>(c, 10 + sub, ws, &s_base);
+#pragma unroll 1
+  for (int sub = 1; sub >= 0; sub--) fast_class<16>(c, 8 + sub, ws, &s_base);
+#pragma unroll 1
+  for (int sub = 1; sub >= 0; sub--) fast_class<8>(c, 6 + sub, ws, &s_base);
+#pragma unroll 1
+  for (int sub = 1; sub >= 0; sub--) fast_class<4>(c, 4 + sub, ws, &s_base);
+#pragma unroll 1
+  for (int sub = 1; sub >= 0; sub--) fast_class<2>(c, 2 + sub, ws, &s_base);
+#pragma unroll 1
+  for (int sub = 1; sub >= 0; sub--) fast_class<1>(c, sub, ws, &s_base);
 }
 
 /* launch shapes of k_expand_fast: (threads per block, blocks per SM) */
@@ -708,7 +714,7 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     }
     if (int rc = dev_reserve(ctx, ctx->states, sizeof(SeqState) * (size_t)wave)) return fail(rc);
     if (int rc = dev_reserve(ctx, ctx->tasks, sizeof(int32_t) * 2 * (size_t)qcap)) return fail(rc);
-    if (int rc = dev_reserve(ctx, ctx->ftasks, sizeof(int32_t) * 2 * RF_FAST_CLASSES * (size_t)(fcap + 1))) return fail(rc);
+    if (int rc = dev_reserve(ctx, ctx->ftasks, sizeof(int32_t) * 2 * RF_FAST_LISTS * (size_t)(fcap + 1))) return fail(rc);
     if (int rc = dev_reserve(ctx, ctx->scratch, (size_t)qcap * (size_t)caps.wscratch_bytes)) return fail(rc);
     if (int rc = dev_reserve(ctx, ctx->small, 256)) return fail(rc);
     WaveCtx wc;
@@ -723,7 +729,7 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     wc.Q.n_fast = (int32_t *)ctx->small.p + 2; wc.Q.fast_cap = (int32_t)fcap; wc.Q.fast_task = (int32_t *)ctx->ftasks.p;
     wc.Q.fast_lv = fastcfg.L_cap; wc.Q.fast_br = fastcfg.br_cap;
     wc.fast = fastcfg;
-    wc.fast_next = (int32_t *)ctx->small.p + 2 + RF_FAST_CLASSES;
+    wc.fast_next = (int32_t *)ctx->small.p + 2 + RF_FAST_LISTS;
     const FastShape &fsh = g_fast_shapes[ctx->fast_shape];
     const size_t fast_smem = (size_t)(fsh.threads / 32) * (size_t)fastcfg.smem_per_warp;
     /* a branch of a loop covers at least min_hp + 2 positions */
@@ -763,7 +769,7 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
       k_init<<<nw, T, 0, ctx->stream>>>(wc);
       launches++;
       for (int it = 0;; it++) {
-        CK(cudaMemsetAsync(ctx->small.p, 0, 64, ctx->stream));
+        CK(cudaMemsetAsync(ctx->small.p, 0, 128, ctx->stream)); /* n_tasks, n_active, list counters, list cursors */
         k_gather<<<nw, T, 0, ctx->stream>>>(wc);
         launches++;
         if (fcap > 0) {
