@@ -274,10 +274,11 @@ def run_b200(args, wl):
     for _ in range(min(args.warmup, 2)):
         step_host()
     barrier()
-    e2e_s, h2d, d2h = 0.0, 0, 0
+    e2e_s, h2d, d2h, e2e_steps = 0.0, 0, 0, []
     for _ in range(args.steps):
         dt, raw = step_host()
         e2e_s += dt
+        e2e_steps.append(round(dt * 1e3, 3))
         h2d, d2h = raw.h2d_bytes, raw.d2h_bytes
     barrier()
 
@@ -323,7 +324,7 @@ def run_b200(args, wl):
             "wall_ms_per_step_device_inputs": wall_dev_max / args.steps * 1e3,
             "e2e": {"value": n_total * args.steps / e2e_max, "unit": UNIT,
                     "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": d2h_all,
-                    "ms_per_step": e2e_max / args.steps * 1e3},
+                    "ms_per_step": e2e_max / args.steps * 1e3, "ms_steps_rank0": e2e_steps},
             "gpu_launches": launches_all,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
