@@ -498,6 +498,7 @@ __device__ __forceinline__ void fast_p7(RF_FAST_ARGS) {
     off = __shfl_sync(FULL, off, 0);
     if (off >= 0) {
       Cand *cand = (Cand *)(arena + aoff.cand) + off;
+      CandKid *ckid = (CandKid *)(arena + aoff.ckid) + off;
       for (int at = lane; at < keep_n; at += 32) {
         const uint32_t key = ~ck[at];
         const int r = (int)(key & 255u);
@@ -506,8 +507,9 @@ __device__ __forceinline__ void fast_p7(RF_FAST_ARGS) {
         Cand &c = cand[at];
         c.dE = (int32_t)(key >> 8) - 0x800000;
         c.mip = (uint16_t)mip; c.mjp = (uint16_t)mjp; c.nb = (uint16_t)nb; c.rank = (uint16_t)r;
-        c.inner_id = (mjp - mip > 1) ? -1 : -2;                       /* rafft.py:130 */
-        c.outer_id = (mip - (nb - 1) > 0 || mjp + nb < lv) ? -1 : -2; /* rafft.py:141 */
+        c.pad_ = 0;
+        ckid[at].inner_id = (mjp - mip > 1) ? -1 : -2;                       /* rafft.py:130 */
+        ckid[at].outer_id = (mip - (nb - 1) > 0 || mjp + nb < lv) ? -1 : -2; /* rafft.py:141 */
         uint64_t flo = 0, fhi = 0;
         for (int k = 0; k < nb; k++) {
           uint64_t l1, h1;

@@ -91,11 +91,18 @@ struct NodeRec {
   int32_t nht_slot, pad_;   /* slot in the unique-loop table (for the clean-up) */
 };
 
+/* One stem of a region: exactly one 32-byte sector, 32-byte aligned, so that the product
+ * enumeration (one random record per region and combination) costs one sector per look-up.
+ * The child loop ids, which only the selected children need, live in Arena::ckid. */
 struct Cand {
   int32_t dE;
   uint16_t mip, mjp, nb, rank;
-  int32_t inner_id, outer_id; /* -1 unresolved, -2 no such node, -3 being created */
+  int32_t pad_;
   uint64_t fp_lo, fp_hi;      /* sum of pair fingerprints of the stem */
+};
+static_assert(sizeof(Cand) == 32, "Cand is one sector");
+struct CandKid {
+  int32_t inner_id, outer_id; /* -1 unresolved, -2 no such node, -3 being created */
 };
 
 struct StoreRec {  /* a structure that has been in a beam */
@@ -438,6 +445,7 @@ struct Arena {
   NodeRec *node;       /* node_cap */
   int16_t *pool16;     /* pool16_cap: branches + segment offsets of nodes */
   Cand *cand;          /* cand_cap */
+  CandKid *ckid;       /* cand_cap: child loops of the stems */
   StoreRec *store;     /* store_cap */
   char *store_db;      /* store_cap * L */
   int32_t *nlist;      /* nlist_cap: node lists of stored structures */
@@ -546,7 +554,7 @@ RF_HD size_t wscratch_carve(WarpScratch &W, char *base, const Caps &c, const Fol
 RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &fp) {
   size_t off = 0;
 #define RF_CARVE(field, type, count)                              \
-  off = align_up(off, 16);                                        \
+  off = align_up(off, 32);                                        \
   A.field = (type *)(base ? base + off : nullptr);                \
   off += sizeof(type) * (size_t)(count);
   int L = c.L_max;
@@ -558,6 +566,7 @@ RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &
   RF_CARVE(node, NodeRec, c.node_cap);
   RF_CARVE(pool16, int16_t, c.pool16_cap);
   RF_CARVE(cand, Cand, c.cand_cap);
+  RF_CARVE(ckid, CandKid, c.cand_cap);
   RF_CARVE(store, StoreRec, c.store_cap);
   RF_CARVE(store_db, char, (size_t)c.store_cap * (size_t)((L + 15) & ~15)); /* rows padded to 16 bytes */
   RF_CARVE(nlist, int32_t, c.nlist_cap);
@@ -581,7 +590,7 @@ RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &
 }
 /* Byte offsets of the arena pieces (computed once on the host, bound per block/warp). */
 struct ArenaOff {
-  uint32_t seen, nht, code, node, pool16, cand, store, store_db, nlist, ncnt, ncoff, seen_used, fresh, sel, sel_idx, sel_store, beam, traj_n, traj, todo, todo_id, flag, pref, sel_e;
+  uint32_t seen, nht, code, node, pool16, cand, ckid, store, store_db, nlist, ncnt, ncoff, seen_used, fresh, sel, sel_idx, sel_store, beam, traj_n, traj, todo, todo_id, flag, pref, sel_e;
 };
 RF_HD void arena_bind(Arena &A, char *base, const ArenaOff &o) {
   A.seen = (SeenEnt *)(base + o.seen);
@@ -590,6 +599,7 @@ RF_HD void arena_bind(Arena &A, char *base, const ArenaOff &o) {
   A.node = (NodeRec *)(base + o.node);
   A.pool16 = (int16_t *)(base + o.pool16);
   A.cand = (Cand *)(base + o.cand);
+  A.ckid = (CandKid *)(base + o.ckid);
   A.store = (StoreRec *)(base + o.store);
   A.store_db = (char *)(base + o.store_db);
   A.nlist = (int32_t *)(base + o.nlist);
@@ -620,6 +630,7 @@ inline void arena_offsets(ArenaOff &o, const Caps &c, const FoldParams &fp) {
   o.node = (uint32_t)((char *)A.node - base);
   o.pool16 = (uint32_t)((char *)A.pool16 - base);
   o.cand = (uint32_t)((char *)A.cand - base);
+  o.ckid = (uint32_t)((char *)A.ckid - base);
   o.store = (uint32_t)((char *)A.store - base);
   o.store_db = (uint32_t)((char *)A.store_db - base);
   o.nlist = (uint32_t)((char *)A.nlist - base);
@@ -1090,9 +1101,10 @@ struct Fold {
         const uint32_t ij = W.r_stem[r];
         const int mip = ij >> 16, mjp = ij & 0xffff, nb = W.r_nb[r];
         c.dE = W.r_dE[r]; c.mip = (uint16_t)mip; c.mjp = (uint16_t)mjp; c.nb = (uint16_t)nb;
-        c.rank = (uint16_t)r;
-        c.inner_id = (mjp - mip > 1) ? -1 : -2;                       /* rafft.py:130 */
-        c.outer_id = (mip - (nb - 1) > 0 || mjp + nb < lv) ? -1 : -2; /* rafft.py:141 */
+        c.rank = (uint16_t)r; c.pad_ = 0;
+        CandKid &ck = A.ckid[off + at];
+        ck.inner_id = (mjp - mip > 1) ? -1 : -2;                       /* rafft.py:130 */
+        ck.outer_id = (mip - (nb - 1) > 0 || mjp + nb < lv) ? -1 : -2; /* rafft.py:141 */
         uint64_t flo = 0, fhi = 0;
         for (int k = 0; k < nb; k++) {
           uint64_t l1, h1;
@@ -1144,20 +1156,39 @@ struct Fold {
    * itertools.product over the nodes that have candidates, last list varies fastest */
   RF_FN void combo_eval(const StoreRec &S, uint64_t combo, int &e, uint64_t &lo, uint64_t &hi) const {
     e = S.e; lo = S.fp_lo; hi = S.fp_hi;
-    for (int k = S.nl_n - 1; k >= 0; k--) {
-      const uint32_t c = (uint32_t)A.ncnt[S.nl_off + k];
-      if (c == 0) continue;
-      uint32_t dgt = 0;
-      if (c != 1) {
-        if ((combo >> 32) == 0) { /* the usual case: 32-bit division */
-          const uint32_t c32 = (uint32_t)combo, q = c32 / c;
-          dgt = c32 - q * c; combo = q;
-        } else {
-          dgt = (uint32_t)(combo % c); combo /= c;
+    /* four regions at a time: the digits are decoded first, then the four stem records are
+     * fetched together (independent loads in flight instead of one load latency per region) */
+    for (int k0 = S.nl_n - 1; k0 >= 0; k0 -= 4) {
+      int at[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int k = k0 - j;
+        at[j] = -1;
+        const uint32_t c = k >= 0 ? (uint32_t)A.ncnt[S.nl_off + k] : 0u;
+        if (c == 0) continue;
+        uint32_t dgt = 0;
+        if (c != 1) {
+          if ((combo >> 32) == 0) { /* the usual case: 32-bit division */
+            const uint32_t c32 = (uint32_t)combo, q = c32 / c;
+            dgt = c32 - q * c; combo = q;
+          } else {
+            dgt = (uint32_t)(combo % c); combo /= c;
+          }
+        }
+        at[j] = A.ncoff[S.nl_off + k] + (int)dgt;
+      }
+      int de[4];
+      uint64_t l[4], h[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        de[j] = 0; l[j] = 0; h[j] = 0;
+        if (at[j] >= 0) {
+          const Cand &cd = A.cand[at[j]];
+          de[j] = cd.dE; l[j] = cd.fp_lo; h[j] = cd.fp_hi;
         }
       }
-      const Cand &cd = A.cand[A.ncoff[S.nl_off + k] + dgt];
-      e += cd.dE; lo += cd.fp_lo; hi += cd.fp_hi;
+#pragma unroll
+      for (int j = 0; j < 4; j++) { e += de[j]; lo += l[j]; hi += h[j]; }
     }
     if (lo == 0) lo = 1; /* 0 marks an empty slot of the seen table */
   }
@@ -1640,7 +1671,7 @@ struct Fold {
           const NodeRec &nd = A.node[v];
           int dgt = (int)(combo % (uint64_t)c);
           combo /= (uint64_t)c;
-          Cand &cd = A.cand[nd.cand_off + dgt];
+          CandKid &cd = A.ckid[nd.cand_off + dgt];
           for (int side = 0; side < 2; side++) {
             int *idp = side ? &cd.outer_id : &cd.inner_id;
             if (*idp == -2) continue;
@@ -1687,7 +1718,7 @@ struct Fold {
     RF_PAR_BEGIN(a, n_todo)
       int id = nht_resolve(node_base + a);
       if (id < 0) fail(ST_ERR_CAPACITY);
-      Cand &cd = A.cand[A.node[A.todo[3 * a]].cand_off + A.todo[3 * a + 1]];
+      CandKid &cd = A.ckid[A.node[A.todo[3 * a]].cand_off + A.todo[3 * a + 1]];
       if (A.todo[3 * a + 2]) cd.outer_id = id; else cd.inner_id = id;
     RF_PAR_END
     if (sh->status != ST_OK) { finish_fold(); return; }
@@ -1753,8 +1784,9 @@ struct Fold {
           int dgt = (int)(combo % (uint64_t)c);
           combo /= (uint64_t)c;
           const Cand &cd = A.cand[nd.cand_off + dgt];
-          if (cd.outer_id != -2) A.nlist[--w] = cd.outer_id;
-          if (cd.inner_id != -2) A.nlist[--w] = cd.inner_id;
+          const CandKid &kid = A.ckid[nd.cand_off + dgt];
+          if (kid.outer_id != -2) A.nlist[--w] = kid.outer_id;
+          if (kid.inner_id != -2) A.nlist[--w] = kid.inner_id;
           for (int q = 0; q < cd.nb; q++) {
             db[pos_of(nd, cd.mip - q)] = '(';
             db[pos_of(nd, cd.mjp + q)] = ')';

@@ -616,6 +616,18 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     if (L > L_max) L_max = (int)L;
   }
   const int T = ctx->block_threads;
+  /* per-kernel overrides of the block size (tuning; same results for any value) */
+  auto threads_of = [&](const char *name, int dflt) {
+    const char *e = getenv(name);
+    const int v = e ? atoi(e) : 0;
+    return (v >= 32 && v <= RF_BLOCK_THREADS_MAX && v % 32 == 0) ? v : dflt;
+  };
+  /* measured on B200 (tools/threads_sweep.sh): the product enumeration wants 4 warps per sequence
+   * (more look-ups in flight), selection and materialisation 2 warps up to -ms 100 and 4 beyond */
+  const int T_ms = params->max_stack > 100 && T == 64 ? 128 : T;
+  const int T_gather = threads_of("RAFFT_GATHER_THREADS", T), T_combine = threads_of("RAFFT_COMBINE_THREADS", T == 64 ? 128 : T);
+  const int T_select = threads_of("RAFFT_SELECT_THREADS", T_ms), T_mat = threads_of("RAFFT_MATERIALISE_THREADS", T_ms);
+  const int T_finish = threads_of("RAFFT_FINISH_THREADS", RF_BLOCK_THREADS_MAX);
   ResultImpl *R = new ResultImpl;
   memset(&R->pub, 0, sizeof R->pub);
   R->ctx = ctx;
@@ -770,7 +782,7 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
       launches++;
       for (int it = 0;; it++) {
         CK(cudaMemsetAsync(ctx->small.p, 0, 128, ctx->stream)); /* n_tasks, n_active, list counters, list cursors */
-        k_gather<<<nw, T, 0, ctx->stream>>>(wc);
+        k_gather<<<nw, T_gather, 0, ctx->stream>>>(wc);
         launches++;
         if (fcap > 0) {
           CK(cudaEventRecord(ctx->evx0, ctx->stream));
@@ -786,9 +798,9 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
           k_expand<5><<<egrid, 128, 0, ctx->stream>>>(wc);
           launches += 5;
         }
-        k_combine<<<nw, T, stage_bytes, ctx->stream>>>(wc);
-        k_select<<<nw, T, (size_t)wc.sel_smem, ctx->stream>>>(wc);
-        k_materialise<<<nw, T, 0, ctx->stream>>>(wc);
+        k_combine<<<nw, T_combine, stage_bytes, ctx->stream>>>(wc);
+        k_select<<<nw, T_select, (size_t)wc.sel_smem, ctx->stream>>>(wc);
+        k_materialise<<<nw, T_mat, 0, ctx->stream>>>(wc);
         launches += 3;
         CK(cudaMemcpyAsync(ctx->h_small + 16, (int32_t *)ctx->small.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
         CK(cudaStreamSynchronize(ctx->stream));
@@ -803,7 +815,7 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
         if (hs[1] == 0) break;
         if (it > 100000) { ctx->err = "rafft_fold_batch: no progress"; return fail(RAFFT_ERR_CUDA); }
       }
-      k_finish<<<nw, RF_BLOCK_THREADS_MAX, 0, ctx->stream>>>(wc);
+      k_finish<<<nw, T_finish, 0, ctx->stream>>>(wc);
       launches++;
       if (dbg) { /* high-water marks of the arena pieces against their capacities */
         std::vector<SeqState> hs((size_t)nw);
