@@ -62,6 +62,7 @@ struct FoldParams {
   double w[4][4];   /* pair weights as the reference's float64 (prep_sequence CENCODING) */
   int32_t wi[4][4]; /* same * 16, exact integers (host checks) */
   int32_t cand_thr; /* keep stems with dE < cand_thr (dcal); exact test per structure later */
+  int32_t seen_gen; /* 1..65535: generation tag of this fold's entries of the `seen` table */
 };
 
 /* Capacities of one per-block arena (host sizes them; overflow -> status, host regrows). */
@@ -438,7 +439,10 @@ RF_NOINLINE int loop_energy(const EnergyView &ev, int ci, int cj, const int16_t 
 }
 /* ------------------------------------------------------------------------------------ */
 /* Per-block working memory, carved from one arena (global memory, L1/L2 resident).       */
-struct SeenEnt { uint64_t lo, hi; };
+/* `seen` entry: 64 + 48 bits of the structure fingerprint and, in the top 16 bits of `hi`, the
+ * generation of the fold that wrote it -- entries of earlier folds of the arena read as empty,
+ * so the table needs no clean-up pass (the host zeroes it when the generation counter wraps). */
+struct alignas(16) SeenEnt { uint64_t lo, hi; };
 
 struct Arena {
   uint8_t *code;       /* L_max */
@@ -452,7 +456,6 @@ struct Arena {
   int32_t *ncnt;       /* nlist_cap: candidates of that node passing for the owning structure */
   int32_t *ncoff;      /* nlist_cap: first candidate record of that node (copy of NodeRec::cand_off) */
   SeenEnt *seen;       /* seen_cap; lo == 0 marks an empty slot (kept clean between runs) */
-  int32_t *seen_used;  /* seen_cap: occupied slots, for the clean-up */
   unsigned long long *nht;     /* nht_cap: (hash32 << 32) | (node id + 1), 0 = empty */
   NewRec *fresh;       /* new_cap */
   int32_t *sel;        /* max_stack: selected entries of the next beam */
@@ -572,7 +575,6 @@ RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &
   RF_CARVE(nlist, int32_t, c.nlist_cap);
   RF_CARVE(ncnt, int32_t, c.nlist_cap);
   RF_CARVE(ncoff, int32_t, c.nlist_cap);
-  RF_CARVE(seen_used, int32_t, c.seen_cap);
   RF_CARVE(fresh, NewRec, c.new_cap);
   RF_CARVE(sel, int32_t, fp.max_stack);
   RF_CARVE(sel_idx, int32_t, fp.max_stack);
@@ -590,7 +592,7 @@ RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &
 }
 /* Byte offsets of the arena pieces (computed once on the host, bound per block/warp). */
 struct ArenaOff {
-  uint32_t seen, nht, code, node, pool16, cand, ckid, store, store_db, nlist, ncnt, ncoff, seen_used, fresh, sel, sel_idx, sel_store, beam, traj_n, traj, todo, todo_id, flag, pref, sel_e;
+  uint32_t seen, nht, code, node, pool16, cand, ckid, store, store_db, nlist, ncnt, ncoff, fresh, sel, sel_idx, sel_store, beam, traj_n, traj, todo, todo_id, flag, pref, sel_e;
 };
 RF_HD void arena_bind(Arena &A, char *base, const ArenaOff &o) {
   A.seen = (SeenEnt *)(base + o.seen);
@@ -605,7 +607,6 @@ RF_HD void arena_bind(Arena &A, char *base, const ArenaOff &o) {
   A.nlist = (int32_t *)(base + o.nlist);
   A.ncnt = (int32_t *)(base + o.ncnt);
   A.ncoff = (int32_t *)(base + o.ncoff);
-  A.seen_used = (int32_t *)(base + o.seen_used);
   A.fresh = (NewRec *)(base + o.fresh);
   A.sel = (int32_t *)(base + o.sel);
   A.sel_idx = (int32_t *)(base + o.sel_idx);
@@ -636,7 +637,6 @@ inline void arena_offsets(ArenaOff &o, const Caps &c, const FoldParams &fp) {
   o.nlist = (uint32_t)((char *)A.nlist - base);
   o.ncnt = (uint32_t)((char *)A.ncnt - base);
   o.ncoff = (uint32_t)((char *)A.ncoff - base);
-  o.seen_used = (uint32_t)((char *)A.seen_used - base);
   o.fresh = (uint32_t)((char *)A.fresh - base);
   o.sel = (uint32_t)((char *)A.sel - base);
   o.sel_idx = (uint32_t)((char *)A.sel_idx - base);
@@ -1128,24 +1128,32 @@ struct Fold {
   }
 
   /* --- seen set (global per sequence, rafft.py:196-200) ------------------------------- */
+  RF_FN uint64_t seen_tag(uint64_t hi) const {
+    return (hi & 0x0000ffffffffffffULL) | ((uint64_t)(uint32_t)prm.seen_gen << 48);
+  }
   RF_FN bool seen_has(uint64_t lo, uint64_t hi) const {
+    const uint64_t th = seen_tag(hi), gen = (uint64_t)(uint32_t)prm.seen_gen;
     unsigned mask = caps.seen_cap - 1;
     unsigned slot = (unsigned)(lo ^ (hi >> 7)) & mask;
     for (;;) {
-      uint64_t l = A.seen[slot].lo;
-      if (l == 0) return false;
-      if (l == lo && A.seen[slot].hi == hi) return true;
+      const SeenEnt en = A.seen[slot];
+      if ((en.hi >> 48) != gen) return false;
+      if (en.lo == lo && en.hi == th) return true;
       slot = (slot + 1) & mask;
     }
   }
+  /* never concurrent with seen_has (block barriers separate the phases); two inserts of one
+   * phase carry different fingerprints (the in-chunk table removed the duplicates) */
   RF_FN void seen_put(uint64_t lo, uint64_t hi) {
+    const uint64_t th = seen_tag(hi), gen = (uint64_t)(uint32_t)prm.seen_gen;
     unsigned mask = caps.seen_cap - 1;
     unsigned slot = (unsigned)(lo ^ (hi >> 7)) & mask;
     for (;;) {
-      if (A.seen[slot].lo == 0 &&
-          Exec::atomic_cas64((unsigned long long *)&A.seen[slot].lo, 0ULL, lo) == 0ULL) {
-        A.seen[slot].hi = hi;
-        A.seen_used[Exec::atomic_add(&sh->n_seen, 1)] = (int32_t)slot;
+      const unsigned long long cur = A.seen[slot].hi;
+      if ((cur >> 48) != gen &&
+          Exec::atomic_cas64((unsigned long long *)&A.seen[slot].hi, cur, th) == cur) {
+        A.seen[slot].lo = lo;
+        Exec::atomic_add(&sh->n_seen, 1);
         return;
       }
       slot = (slot + 1) & mask;
@@ -1268,22 +1276,8 @@ struct Fold {
   /* ---- phase: results out, hash tables left empty for the next sequence of this arena ---- */
   RF_FN void phase_finish(OutBuf &out) {
     emit(out);
-    /* leave the two hash tables empty for the next sequence of this arena */
-    {
-      /* four independent slot look-ups in flight per thread */
-      const int n_seen = sh->n_seen;
-      Exec::sync();
-      for (int i = Exec::tid(); i < n_seen; i += 4 * Exec::stride()) {
-        int idx[4];
-        for (int q = 0; q < 4; q++) {
-          const int j = i + q * Exec::stride();
-          idx[q] = j < n_seen ? A.seen_used[j] : -1;
-        }
-        for (int q = 0; q < 4; q++)
-          if (idx[q] >= 0) { A.seen[idx[q]].lo = 0; A.seen[idx[q]].hi = 0; }
-      }
-      Exec::sync();
-    }
+    /* leave the unique-loop table empty for the next sequence of this arena (the `seen` table
+     * is generation-tagged and needs no clean-up) */
     RF_PAR_BEGIN(i, sh->n_node)
       int s = A.node[i].nht_slot;
       if (s >= 0) A.nht[s] = 0;

@@ -127,6 +127,7 @@ inline bool build_fold_params(const rafft_params *p, FoldParams *F, std::string 
   for (int a = 0; a < 4; a++)
     for (int b = 0; b < 4; b++) F->wi[a][b] = (int32_t)(F->w[a][b] * 16.0);
   F->cand_thr = p->min_nrj == 0.0 ? 0 : (int32_t)ceil(p->min_nrj * 100.0) + 2;
+  F->seen_gen = 1; /* the caller advances it per fold of an arena */
   return true;
 }
 

@@ -403,6 +403,7 @@ struct rafft_ctx {
   int use_fast = 1;         /* shared-memory expansion for small regions (RAFFT_FAST=0 disables) */
   uint64_t arena_sig = 0;   /* layout of the arenas whose hash tables are known to be empty */
   bool arena_dirty = true;
+  uint32_t seen_gen = 0;    /* generation of the last fold in the arenas (tag of its `seen` entries) */
   size_t arena_clean = 0;   /* leading bytes of the arena buffer known to be clean */
   std::string err;
 };
@@ -778,6 +779,13 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
       const int nw = (int)std::min<int64_t>(wave, m - w0);
       wc.order = (const int32_t *)ctx->order.p + w0;
       wc.n = nw;
+      /* every fold of an arena tags its `seen` entries with a new generation; when the 16-bit
+       * counter wraps the tables are zeroed once */
+      if (++ctx->seen_gen > 65535u) {
+        CK(cudaMemsetAsync(ctx->arenas.p, 0, ctx->arena_clean, ctx->stream));
+        ctx->seen_gen = 1;
+      }
+      wc.prm.seen_gen = (int32_t)ctx->seen_gen;
       k_init<<<nw, T, 0, ctx->stream>>>(wc);
       launches++;
       for (int it = 0;; it++) {

@@ -68,6 +68,12 @@ int emu_fold(const rafft_energy_params *ep_in, const char *seq, int L, const raf
   out.db = db.data(); out.step_n = step_n.data(); out.entries = entries.data(); out.cursors = cursors;
   out.struct_cap = scap; out.db_cap = (int64_t)db.size(); out.step_cap = caps.step_cap; out.entry_cap = ecap;
   /* the host loop of rafft_cuda.cu, for one sequence: rounds of phase "kernels" */
+  /* two folds in the same arena: the second one (the one reported) meets the `seen` entries the
+   * first one left behind under another generation tag */
+  for (int gen = 1; gen <= 2; gen++) {
+  F.seen_gen = gen;
+  n_tasks = 0;
+  cursors[0] = cursors[1] = cursors[2] = cursors[3] = cursors[4] = cursors[5] = cursors[6] = cursors[7] = 0;
   f.phase_init(seq, L, 0);
   for (int round = 0; sh.active; round++) {
     n_tasks = 0;
@@ -83,11 +89,13 @@ int emu_fold(const rafft_energy_params *ep_in, const char *seq, int L, const raf
     if (round > 100000) { fprintf(stderr, "emu_fold: no progress\n"); return -3; }
   }
   f.phase_finish(out);
-  /* run() must leave the hash tables empty for the next sequence of the arena */
+  /* a fold must leave the unique-loop table empty for the next sequence of the arena (the
+   * `seen` table in front of it is generation-tagged instead) */
   {
-    size_t tb = arena_table_bytes(caps);
-    for (size_t k = 0; k < tb; k++)
-      if (arena[k]) { fprintf(stderr, "emu_fold: hash tables not clean after run\n"); return -2; }
+    size_t t0 = (size_t)((char *)f.A.nht - arena.data()), tb = sizeof(unsigned long long) * (size_t)caps.nht_cap;
+    for (size_t k = t0; k < t0 + tb; k++)
+      if (arena[k]) { fprintf(stderr, "emu_fold: unique-loop table not clean after run\n"); return -2; }
+  }
   }
   if (status[0] == ST_ERR_CAPACITY && getenv("EMU_VERBOSE")) fprintf(stderr, "emu_fold: capacity exceeded at fold_core.cuh line %d\n", -sh.fail_line < 0 ? sh.fail_line : -sh.fail_line);
   if (cnt) for (int k = 0; k < CNT_N; k++) cnt[k] = counters[k];
