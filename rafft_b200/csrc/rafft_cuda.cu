@@ -537,6 +537,8 @@ int rafft_create(rafft_ctx **out, int cuda_device, const rafft_energy_params *ep
     CK(cudaHostAlloc((void **)&ctx->h_small, 64 * sizeof(int64_t), cudaHostAllocDefault));
     const char *s = getenv("RAFFT_BLOCK_THREADS");
     if (s) { int v = atoi(s); if (v >= 32 && v <= RF_BLOCK_THREADS_MAX && v % 32 == 0) ctx->block_threads = v; }
+    s = getenv("RAFFT_SEEN_GEN0"); /* tests: start near the wrap of the `seen` generation counter */
+    if (s) { int v = atoi(s); if (v >= 0 && v <= 65535) ctx->seen_gen = (uint32_t)v; }
     s = getenv("RAFFT_BLOCKS_PER_SM");
     if (s) { int v = atoi(s); if (v >= 1 && v <= 32) ctx->blocks_per_sm = v; }
     s = getenv("RAFFT_MAX_WAVE");

@@ -278,3 +278,32 @@ def test_cfg5_fold_then_kinetics(ctx, oracle):
     assert len(times) == 101 and len(struct_list) == len({st.str_struct for step in traj for st in step})
     early = np.asarray(pops[50], dtype=np.float64)
     assert abs(early.sum() - 1.0) < 1e-9 and early.min() > -1e-6
+
+
+def test_seen_generation_wrap(oracle):
+    """The `seen` table is generation-tagged (no clean-up between folds of an arena): folds that
+    reuse the arenas, across the wrap of the 16-bit generation counter, stay bit-exact."""
+    code = r'''
+import sys, numpy as np
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+import pyoracle
+from rafft_b200 import rafft as R
+from rafft_b200.synth import splitmix_seq
+ctx = R.FoldContext(0)
+seqs = [splitmix_seq(900 + k, 40 + 7 * k) for k in range(24)]
+want, _ = pyoracle.fold_batch(seqs, 100, 20, 1000)
+offs = np.zeros(len(seqs) + 1, dtype=np.int64); np.cumsum([len(s) for s in seqs], out=offs[1:])
+prm = R.make_params(100, 20, 1000, traj=True)
+for rep in range(5):                      # generations 65534, 65535, wrap -> 1, 2, 3
+    order = seqs if rep %% 2 == 0 else seqs[::-1]
+    o = np.zeros(len(order) + 1, dtype=np.int64); np.cumsum([len(s) for s in order], out=o[1:])
+    raw = ctx.fold_raw("".join(order).encode(), o, prm)
+    assert (raw.status == 0).all()
+    w = want if rep %% 2 == 0 else want[::-1]
+    for i in range(len(order)):
+        assert raw.steps(i) == w[i], (rep, i)
+print("ok")
+''' % (ROOT, os.path.join(ROOT, "oracle"))
+    env = dict(os.environ, RAFFT_SEEN_GEN0="65533")
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env)
+    assert out.returncode == 0 and out.stdout.strip() == "ok", out.stderr[-2000:]
