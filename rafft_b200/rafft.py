@@ -53,7 +53,7 @@ class FoldContext:
                                         n, C.byref(params), C.byref(res))
         if rc != N.RAFFT_OK:
             raise self._err(rc)
-        return RawResult(res, offs, self._lib)
+        return RawResult(res, offs, self._lib, self)
 
     def fold_raw_device(self, d_seqs_ptr, d_offs_ptr, n, total_len, max_len, params):
         """Inputs already on this context's device (raw device pointers)."""
@@ -62,7 +62,7 @@ class FoldContext:
                                                n, total_len, max_len, C.byref(params), C.byref(res))
         if rc != N.RAFFT_OK:
             raise self._err(rc)
-        return RawResult(res, None, self._lib)
+        return RawResult(res, None, self._lib, self)
 
     def eval_structures(self, seqs, structs):
         "integer energies (dcal/mol) of whole structures; replaces fold_compound.eval_structure"
@@ -92,8 +92,9 @@ class RawResult:
     """Arrays of one rafft_result (see include/rafft_b200.h), as zero-copy views of the memory the
     library owns; close() (or garbage collection) calls rafft_result_free."""
 
-    def __init__(self, res, offs, lib):
+    def __init__(self, res, offs, lib, owner=None):
         self._res, self._lib = res, lib
+        self._owner = owner  # the result hands its pinned block back to this context: keep it alive
         r = res.contents
         n = r.n_seq
         self.n_seq = n
@@ -122,7 +123,9 @@ class RawResult:
     def close(self):
         "hand the arrays back to the library; the views must not be used afterwards"
         if self._res is not None:
-            self._lib.rafft_result_free(self._res)
+            # a result outliving its (explicitly closed) context is dropped, not handed back
+            if self._owner is None or self._owner._h.value:
+                self._lib.rafft_result_free(self._res)
             self._res = None
 
     def __del__(self):

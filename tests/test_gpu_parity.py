@@ -302,6 +302,8 @@ for rep in range(5):                      # generations 65534, 65535, wrap -> 1,
     w = want if rep %% 2 == 0 else want[::-1]
     for i in range(len(order)):
         assert raw.steps(i) == w[i], (rep, i)
+    raw.close()
+ctx.close()
 print("ok")
 ''' % (ROOT, os.path.join(ROOT, "oracle"))
     env = dict(os.environ, RAFFT_SEEN_GEN0="65533")
