@@ -41,7 +41,7 @@ WORKLOADS = {
 }
 # dram__bytes_read.sum + dram__bytes_write.sum of k_expand_fast per launch (average over the launches
 # of one step) from the ncu --set full capture under profiles/ (null until one exists for the workload)
-TRAFFIC = {"cfg2": 51.7e6}  # profiles/r01_dram_v12.txt: 672 MB over the 13 launches of one fold
+TRAFFIC = {"cfg2": 51.7e6}  # profiles/r01_dram_v13.txt: 672 MB over the 13 launches of one fold
 METRIC = "sequences folded/sec"
 UNIT = "seq/s"
 
