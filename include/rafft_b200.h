@@ -102,9 +102,20 @@ typedef struct rafft_result {
   double kernel_ms;             /* device time of the fold kernel(s), CUDA events */
   int64_t kernel_launches;      /* number of kernel launches this call made */
   int64_t h2d_bytes, d2h_bytes; /* bytes copied host->device / device->host by this call */
-  double expand_ms;             /* device time of the region-expansion kernel launches alone */
-  int64_t expand_launches;      /* ... and how many of them there were */
+  double expand_ms;             /* device time of the region-expansion kernel launches alone ... */
+  int64_t expand_launches;      /* ... and how many of them there were (profile mode only, else 0) */
+  int64_t iterations;           /* folding iterations of the longest-running lane */
+  /* per kernel family, CUDA events around every launch (filled in profile mode, rafft_set_option
+   * "profile"; zero otherwise): RAFFT_FAM_* */
+  double family_ms[8];
+  int64_t family_launches[8];
+  int32_t lanes;                /* concurrent sub-batches (streams) the call was split into */
+  int32_t loop_mode;            /* 0 one CUDA-graph launch per fold (device-side WHILE), 1 stream launches
+                                   with bounded look-ahead, 2 stepwise (profile mode) */
 } rafft_result;
+
+enum { RAFFT_FAM_GATHER = 0, RAFFT_FAM_EXPAND_FAST, RAFFT_FAM_EXPAND_GENERIC, RAFFT_FAM_COMBINE,
+       RAFFT_FAM_SELECT, RAFFT_FAM_MATERIALISE, RAFFT_FAM_ADVANCE, RAFFT_FAM_OTHER };
 
 typedef struct rafft_ctx rafft_ctx;
 
@@ -125,6 +136,15 @@ const char *rafft_last_error(const rafft_ctx *ctx);
 int rafft_fold_batch(rafft_ctx *ctx, const char *seqs, const int64_t *offs, int32_t n,
                      const rafft_params *params, rafft_result **out);
 void rafft_result_free(rafft_result *res);
+
+/* The same batch folded by several devices of one box from ONE host process: ctxs[0..n_ctx) are
+ * contexts of different CUDA devices; the sequences are dealt to them as contiguous ranges of equal
+ * estimated cost (the path has no exchange step: SURVEY.md section 8e), every device folds its range
+ * on its own host thread and stream and copies its part straight into the one result, which is in
+ * input order and owned by ctxs[0].  Replaces the reference's process pool over the sequences of a
+ * set (benchmark_results/bench_fft.py:17-22).  rafft_fold_batch is the n_ctx = 1 case. */
+int rafft_fold_batch_multi(rafft_ctx *const *ctxs, int32_t n_ctx, const char *seqs, const int64_t *offs,
+                           int32_t n, const rafft_params *params, rafft_result **out);
 
 /* Same, but the inputs already live in device memory (d_seqs: the concatenated letters,
  * d_offs: n+1 int64) and the timed work is the kernel only; results are still returned on
@@ -158,6 +178,16 @@ int rafft_kin_graph(rafft_ctx *ctx, const char *db, int32_t L, const int64_t *st
  * dist[a * n + b] = number of base pairs present in exactly one of the structures a and b
  * (symmetric, zero diagonal).  Errors as rafft_kin_graph. */
 int rafft_bp_distance_matrix(rafft_ctx *ctx, const char *db, int32_t n, int32_t L, int32_t *dist);
+
+/* Tuning / diagnostics switches of a context: "profile" (1: time every kernel family with CUDA
+ * events, stepwise loop; results unchanged), "lanes" (0 automatic, 1, 2), "loop" (0 graph, 1 stream),
+ * "max_wave", "persist".  Unknown names fail with RAFFT_ERR_ARG. */
+int rafft_set_option(rafft_ctx *ctx, const char *name, int64_t value);
+
+/* Issue-rate microbenchmark on the context's device: warp-instructions per second of a stream of
+ * independent IADD3 (every scheduler of every SM issues every cycle: the issue-slot peak the fold
+ * kernels are measured against, bench.py roofline) and of an IADD3/LOP3 mix.  ~10 ms. */
+int rafft_int_peak(rafft_ctx *ctx, double *issue_warp_inst_per_s, double *mix_warp_inst_per_s);
 
 /* Library/build identification, e.g. "rafft_b200 0.1 sm_100a". */
 const char *rafft_version(void);

@@ -46,6 +46,9 @@ def lib():
                                         C.POINTER(Params), C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int),
                                         C.POINTER(C.c_int64)]
         L.oracle_fold_batch.restype = C.c_int
+        L.oracle_fold_batch_check.argtypes = [C.POINTER(EnergyParams), C.c_char_p, C.POINTER(C.c_int64), C.c_int,
+                                              C.POINTER(Params), C.c_int, C.c_int] + [C.c_void_p] * 10
+        L.oracle_fold_batch_check.restype = C.c_int
         L.oracle_auto_cor.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_double, C.c_double,
                                       C.c_double, C.POINTER(C.c_double)]
         L.oracle_window_slide.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int,
@@ -123,6 +126,29 @@ def fold_batch(seqs, nb_mode=100, max_stack=1, max_branch=1000, min_hp=3, min_nr
             out.append(parse_listing(C.string_at(texts[i]).decode()))
             lib().oracle_free(texts[i])
     return out, cnt
+
+
+def fold_batch_check(seqs, raw, nb_mode=100, max_stack=1, max_branch=1000, min_hp=3, min_nrj=0.0, gc=3.0,
+                     au=2.0, gu=1.0, traj=True, nthreads=None):
+    """Fold `seqs` here and compare every beam (energies, dot-brackets, order) with `raw`, the arrays
+    of a rafft_result (rafft_b200.rafft.RawResult), inside the C++ library -- full batches in the
+    time of the oracle folds.  -> (indices of the sequences that differ, counters[n][CNT_N])."""
+    import numpy as np
+    n = len(seqs)
+    assert raw.n_seq == n
+    offs = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum([len(s) for s in seqs], out=offs[1:])
+    prm = Params(nb_mode, max_stack, max_branch, min_hp, 1, min_nrj, 37.0, gc, au, gu)
+    mism = np.zeros(max(n, 1), dtype=np.int32)
+    cnt = np.zeros((n, CNT_N), dtype=np.int64)
+    arrs = [np.ascontiguousarray(a) for a in (raw.status, raw.struct_off, raw.energy, raw.db_off, raw.db,
+                                              raw.step_off, raw.entry_off, raw.entry_struct)]
+    ptr = lambda a: C.c_void_p(a.ctypes.data)
+    lib().oracle_fold_batch_check(C.byref(default_params()), "".join(seqs).encode(),
+                                  offs.ctypes.data_as(C.POINTER(C.c_int64)), n, C.byref(prm),
+                                  nthreads or os.cpu_count() or 1, 1 if traj else 0,
+                                  *[ptr(a) for a in arrs], ptr(mism), ptr(cnt))
+    return [int(i) for i in np.nonzero(mism[:n])[0]], cnt
 
 
 def auto_cor(seq, pos, gc=3.0, au=2.0, gu=1.0):

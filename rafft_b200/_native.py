@@ -18,7 +18,8 @@ CNT_N = len(COUNTER_NAMES)
 # every symbol include/rafft_b200.h declares (tests check the library exports all of them)
 EXPORTS = ("rafft_version", "rafft_default_energy_params", "rafft_create", "rafft_destroy",
            "rafft_last_error", "rafft_fold_batch", "rafft_fold_batch_device", "rafft_result_free",
-           "rafft_eval_structures", "rafft_kin_graph", "rafft_bp_distance_matrix")
+           "rafft_eval_structures", "rafft_kin_graph", "rafft_bp_distance_matrix",
+           "rafft_fold_batch_multi", "rafft_set_option", "rafft_int_peak")
 
 
 class EnergyParams(C.Structure):
@@ -64,7 +65,17 @@ class Result(C.Structure):
                 ("kernel_ms", C.c_double),
                 ("kernel_launches", C.c_int64),
                 ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
-                ("expand_ms", C.c_double), ("expand_launches", C.c_int64)]
+                ("expand_ms", C.c_double), ("expand_launches", C.c_int64),
+                ("iterations", C.c_int64),
+                ("family_ms", C.c_double * 8), ("family_launches", C.c_int64 * 8),
+                ("lanes", C.c_int32), ("loop_mode", C.c_int32)]
+
+
+FAMILY_NAMES = ("gather", "expand_fast", "expand_generic", "combine", "select", "materialise", "advance", "other")
+# kernel names (as ncu prints them) of every family
+FAMILY_KERNELS = {"gather": ("k_gather",), "expand_fast": ("k_expand_fast",), "expand_generic": ("k_expand",),
+                  "combine": ("k_combine",), "select": ("k_select",), "materialise": ("k_materialise",),
+                  "advance": ("k_advance",), "other": ("k_init", "k_finish", "k_ctl_reset")}
 
 
 class NativeError(RuntimeError):
@@ -101,6 +112,13 @@ def lib():
     L.rafft_fold_batch_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64,
                                           C.c_int32, C.POINTER(Params), C.POINTER(C.POINTER(Result))]
     L.rafft_fold_batch_device.restype = C.c_int
+    L.rafft_fold_batch_multi.argtypes = [C.POINTER(C.c_void_p), C.c_int32, C.c_char_p, C.POINTER(C.c_int64),
+                                         C.c_int32, C.POINTER(Params), C.POINTER(C.POINTER(Result))]
+    L.rafft_fold_batch_multi.restype = C.c_int
+    L.rafft_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
+    L.rafft_set_option.restype = C.c_int
+    L.rafft_int_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.rafft_int_peak.restype = C.c_int
     L.rafft_result_free.argtypes = [C.POINTER(Result)]
     L.rafft_result_free.restype = None
     L.rafft_eval_structures.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_int64),

@@ -10,8 +10,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librafft_b200.so")
 SOURCES = ["rafft_cuda.cu"]
-DEPS = ["rafft_cuda.cu", "fold_core.cuh", "host_common.h", "turner2004.inc",
-        os.path.join("..", "..", "include", "rafft_b200.h")]
+DEPS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h", ".inc"))) + \
+       [os.path.join("..", "..", "include", "rafft_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC", "-diag-suppress", "177,550"]
 

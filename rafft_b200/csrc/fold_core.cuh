@@ -704,7 +704,10 @@ struct Fold {
   EnergyView ev;
   TaskQueue Q;
   CombineStage cs; /* bound by the combine kernel only */
-  RF_HD Fold(const DevEnergy *E_, const FoldParams &p, const Caps &c) : E(E_), prm(p), caps(c) {}
+  int32_t gen;     /* generation tag of this fold's `seen` entries (1..65535); the launch-wide default
+                      can be overridden per fold from device memory, so that a cached launch graph
+                      stays valid from one fold to the next */
+  RF_HD Fold(const DevEnergy *E_, const FoldParams &p, const Caps &c) : E(E_), prm(p), caps(c), gen(p.seen_gen) {}
 
   /* --- node geometry ------------------------------------------------------------------ */
   RF_FN const int16_t *node_br(const NodeRec &n) const { return A.pool16 + n.pool_off; }
@@ -1129,10 +1132,10 @@ struct Fold {
 
   /* --- seen set (global per sequence, rafft.py:196-200) ------------------------------- */
   RF_FN uint64_t seen_tag(uint64_t hi) const {
-    return (hi & 0x0000ffffffffffffULL) | ((uint64_t)(uint32_t)prm.seen_gen << 48);
+    return (hi & 0x0000ffffffffffffULL) | ((uint64_t)(uint32_t)gen << 48);
   }
   RF_FN bool seen_has(uint64_t lo, uint64_t hi) const {
-    const uint64_t th = seen_tag(hi), gen = (uint64_t)(uint32_t)prm.seen_gen;
+    const uint64_t th = seen_tag(hi), gen = (uint64_t)(uint32_t)this->gen;
     unsigned mask = caps.seen_cap - 1;
     unsigned slot = (unsigned)(lo ^ (hi >> 7)) & mask;
     for (;;) {
@@ -1145,7 +1148,7 @@ struct Fold {
   /* never concurrent with seen_has (block barriers separate the phases); two inserts of one
    * phase carry different fingerprints (the in-chunk table removed the duplicates) */
   RF_FN void seen_put(uint64_t lo, uint64_t hi) {
-    const uint64_t th = seen_tag(hi), gen = (uint64_t)(uint32_t)prm.seen_gen;
+    const uint64_t th = seen_tag(hi), gen = (uint64_t)(uint32_t)this->gen;
     unsigned mask = caps.seen_cap - 1;
     unsigned slot = (unsigned)(lo ^ (hi >> 7)) & mask;
     for (;;) {

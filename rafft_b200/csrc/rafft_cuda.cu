@@ -2,11 +2,19 @@
  * rafft_cuda.cu -- the C-ABI library (include/rafft_b200.h) over the sm_100a kernels.
  *
  * Kernels in this file:
- *   fold_kernel    persistent thread blocks; each block pulls the next sequence from a device
- *                  queue and runs the whole fold (fold_core.cuh) out of its own arena
+ *   k_ctl_reset / k_init / k_gather / k_expand_fast / k_expand<1..5> / k_combine / k_select /
+ *   k_materialise / k_advance / k_finish
+ *                  the level-synchronous phase kernels of the fold (fold_core.cuh, expand_fast.cuh).
+ *                  One folding iteration of every sequence of a wave is the chain
+ *                  gather -> expand -> combine -> select -> materialise -> advance; the chain is the
+ *                  body of a CUDA-graph WHILE node whose condition k_advance sets on the device, so a
+ *                  whole fold is ONE graph launch with no host round trip.  The
+ *                  block-scope kernels are persistent: a fixed grid pulls the still-active sequences
+ *                  from a compacted list, so late iterations cost what their few live sequences cost.
  *   scan_kernel    exclusive scans that turn per-sequence counts into the ordered layout
  *   pack_kernel    gathers the bump-allocated results into input order
  *   eval_kernel    whole-structure loop-decomposition energies (rafft_eval_structures)
+ *   int_peak_kernel  IADD3/LOP3 issue-rate microbenchmark (rafft_int_peak: the roofline denominator)
  *
  * There is no CPU fallback: every entry point fails with RAFFT_ERR_CUDA when no device is
  * usable.  Nothing here includes or links anything under oracle/.
@@ -16,7 +24,10 @@
 #include <stdlib.h>
 #include <algorithm>
 #include <chrono>
+#include <condition_variable>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 #include "host_common.h"
 #include "expand_fast.cuh"
@@ -28,6 +39,20 @@ using namespace rafft;
 
 /* ------------------------------------------------------------------------------------ */
 /* kernels                                                                               */
+
+/* Device-resident control block of one fold loop (one per lane). */
+struct LoopCtl {
+  int32_t n_tasks;                   /* generic region work list of this iteration */
+  int32_t n_next;                    /* sequences appended to the next active list */
+  int32_t n_fast[RF_FAST_LISTS];     /* shared-memory expansion work lists */
+  int32_t fast_next[RF_FAST_LISTS];  /* ... and their dynamic cursors */
+  int32_t n_cur;                     /* entries of the current active list */
+  int32_t parity;                    /* current active list = alist[parity] */
+  int32_t iters;                     /* folding iterations run */
+  int32_t seen_gen;                  /* generation tag of this fold's `seen` entries */
+  int32_t work[4];                   /* dynamic cursors of gather / combine / select / materialise */
+  int32_t pad_[28];
+};
 
 /* Everything the phase kernels of one wave need (kernel parameter, constant bank).
  * A wave = `n` sequences folded together; slot j of the wave works on sequence order[j], owns
@@ -47,18 +72,19 @@ struct WaveCtx {
   int32_t n;
   TaskQueue Q;
   FastCfg fast;
-  int32_t *fast_next; /* dynamic work counter of k_expand_fast */
+  LoopCtl *ctl;
+  int32_t *alist;     /* two lists of acap wave slots: the sequences still folding */
+  int32_t acap;
   int32_t sel_smem;   /* bytes of shared memory for the energies under selection (0: global) */
-  int32_t *n_active;
+  int32_t *h_prog;    /* host-mapped: [0] iterations finished, [1] 1 once no sequence is active */
   OutBuf out;
 };
 
 #define RF_WAVE_PARAM const __grid_constant__ WaveCtx c
 
-/* block-scope kernels: one block per wave slot, state staged through shared memory */
+/* block-scope kernels: state of wave slot j staged through shared memory */
 struct BlockBind {
-  __device__ __forceinline__ static bool load(const WaveCtx &c, Fold &f, SeqState *sh, bool need_active) {
-    const int j = blockIdx.x;
+  __device__ __forceinline__ static bool load(const WaveCtx &c, Fold &f, SeqState *sh, int j, bool need_active) {
     SeqState *st = c.states + j;
     if (need_active && !st->active) return false;
     for (int k = threadIdx.x; k < (int)(sizeof(SeqState) / 4); k += blockDim.x) ((int *)sh)[k] = ((const int *)st)[k];
@@ -66,16 +92,45 @@ struct BlockBind {
     f.sh = sh;
     f.Q = c.Q;
     f.Q.self = j;
+    f.gen = c.ctl->seen_gen;
     __syncthreads();
     f.bind_ev();
     return true;
   }
-  __device__ __forceinline__ static void store(const WaveCtx &c, SeqState *sh) {
+  __device__ __forceinline__ static void store(const WaveCtx &c, SeqState *sh, int j) {
     __syncthreads();
-    SeqState *st = c.states + blockIdx.x;
+    SeqState *st = c.states + j;
     for (int k = threadIdx.x; k < (int)(sizeof(SeqState) / 4); k += blockDim.x) ((int *)st)[k] = ((const int *)sh)[k];
   }
 };
+
+/* Persistent block-scope kernels: every block pulls the next still-active wave slot from the
+ * compacted list of this iteration (dynamic cursor `which` of the control block). */
+#define RF_FOR_ACTIVE(which)                                                         \
+  __shared__ int s_slot_;                                                             \
+  const int n_cur_ = c.ctl->n_cur;                                                    \
+  const int32_t *alist_ = c.alist + (size_t)c.ctl->parity * (size_t)c.acap;           \
+  for (;;) {                                                                          \
+    __syncthreads();                                                                  \
+    if (threadIdx.x == 0) {                                                           \
+      const int k_ = atomicAdd(&c.ctl->work[which], 1);                               \
+      s_slot_ = k_ < n_cur_ ? alist_[k_] : -1;                                        \
+    }                                                                                 \
+    __syncthreads();                                                                  \
+    const int j = s_slot_;                                                            \
+    if (j < 0) break;
+#define RF_END_ACTIVE }
+
+/* start of a fold: the control block (one block of 64 threads; plain launch, its arguments
+ * change from fold to fold while the graph of the loop is cached) */
+__global__ void k_ctl_reset(LoopCtl *ctl, int nw, int gen) {
+  const int t = threadIdx.x;
+  if (t < RF_FAST_LISTS) { ctl->n_fast[t] = 0; ctl->fast_next[t] = 0; }
+  if (t < 4) ctl->work[t] = 0;
+  if (t == 0) {
+    ctl->n_tasks = 0; ctl->n_next = 0; ctl->n_cur = nw; ctl->parity = 0; ctl->iters = 0; ctl->seen_gen = gen;
+  }
+}
 
 __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_init(RF_WAVE_PARAM) {
   __shared__ SeqState sh;
@@ -85,52 +140,79 @@ __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_init(RF_WAVE_PARAM) {
   f.sh = &sh;
   const int si = c.order[j];
   const int64_t o = c.offs[si];
-  if (threadIdx.x == 0) sh.seq_off = o;
+  if (threadIdx.x == 0) { sh.seq_off = o; c.alist[j] = j; }
   f.phase_init(c.seqs + o, (int)(c.offs[si + 1] - o), si);
-  BlockBind::store(c, &sh);
+  BlockBind::store(c, &sh, j);
 }
 
 __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_gather(RF_WAVE_PARAM) {
   __shared__ SeqState sh;
-  Fold f(c.E, c.prm, c.caps);
-  if (!BlockBind::load(c, f, &sh, true)) return;
-  f.phase_gather();
-  BlockBind::store(c, &sh);
+  RF_FOR_ACTIVE(0)
+    Fold f(c.E, c.prm, c.caps);
+    if (!BlockBind::load(c, f, &sh, j, true)) continue;
+    f.phase_gather();
+    BlockBind::store(c, &sh, j);
+  RF_END_ACTIVE
 }
 
 __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_combine(RF_WAVE_PARAM) {
   __shared__ SeqState sh;
-  Fold f(c.E, c.prm, c.caps);
   extern __shared__ __align__(16) char combine_smem[];
-  if (!BlockBind::load(c, f, &sh, true)) return;
-  stage_carve(f.cs, combine_smem, c.caps.chunk_cap, c.prm.max_stack);
-  f.phase_combine();
-  BlockBind::store(c, &sh);
+  RF_FOR_ACTIVE(1)
+    Fold f(c.E, c.prm, c.caps);
+    if (!BlockBind::load(c, f, &sh, j, true)) continue;
+    stage_carve(f.cs, combine_smem, c.caps.chunk_cap, c.prm.max_stack);
+    f.phase_combine();
+    BlockBind::store(c, &sh, j);
+  RF_END_ACTIVE
 }
 
 __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_select(RF_WAVE_PARAM) {
   __shared__ SeqState sh;
-  Fold f(c.E, c.prm, c.caps);
   extern __shared__ __align__(16) char select_smem[];
-  if (!BlockBind::load(c, f, &sh, true)) return;
-  if (c.sel_smem) f.A.sel_e = (int32_t *)select_smem;
-  f.phase_select();
-  BlockBind::store(c, &sh);
+  RF_FOR_ACTIVE(2)
+    Fold f(c.E, c.prm, c.caps);
+    if (!BlockBind::load(c, f, &sh, j, true)) continue;
+    if (c.sel_smem) f.A.sel_e = (int32_t *)select_smem;
+    f.phase_select();
+    BlockBind::store(c, &sh, j);
+  RF_END_ACTIVE
 }
 
 __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_materialise(RF_WAVE_PARAM) {
   __shared__ SeqState sh;
-  Fold f(c.E, c.prm, c.caps);
-  if (!BlockBind::load(c, f, &sh, true)) return;
-  f.phase_materialise();
-  if (threadIdx.x == 0 && sh.active) atomicAdd(c.n_active, 1);
-  BlockBind::store(c, &sh);
+  int32_t *next_list = c.alist + (size_t)(c.ctl->parity ^ 1) * (size_t)c.acap;
+  RF_FOR_ACTIVE(3)
+    Fold f(c.E, c.prm, c.caps);
+    if (!BlockBind::load(c, f, &sh, j, true)) continue;
+    f.phase_materialise();
+    if (threadIdx.x == 0 && sh.active) next_list[atomicAdd(&c.ctl->n_next, 1)] = j;
+    BlockBind::store(c, &sh, j);
+  RF_END_ACTIVE
+}
+
+/* end of a folding iteration: the next active list becomes the current one, the work lists and
+ * cursors are cleared, and the loop condition is set (graph WHILE node) / published to the host
+ * (stream mode) */
+__global__ void k_advance(LoopCtl *ctl, int32_t *h_prog, cudaGraphConditionalHandle handle, int use_handle) {
+  const int t = threadIdx.x;
+  if (t < RF_FAST_LISTS) { ctl->n_fast[t] = 0; ctl->fast_next[t] = 0; }
+  if (t < 4) ctl->work[t] = 0;
+  if (t == 0) {
+    const int n = ctl->n_next;
+    ctl->n_cur = n; ctl->n_next = 0; ctl->parity ^= 1; ctl->n_tasks = 0;
+    const int it = ++ctl->iters;
+    if (use_handle) cudaGraphSetConditional(handle, n > 0 ? 1u : 0u);
+    if (n == 0) h_prog[1] = 1;
+    __threadfence_system();
+    h_prog[0] = it;
+  }
 }
 
 __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_finish(RF_WAVE_PARAM) {
   __shared__ SeqState sh;
   Fold f(c.E, c.prm, c.caps);
-  BlockBind::load(c, f, &sh, false);
+  BlockBind::load(c, f, &sh, blockIdx.x, false);
   OutBuf out = c.out;
   f.phase_finish(out);
 }
@@ -167,7 +249,7 @@ __device__ __forceinline__ void fast_class(const WaveCtx &c, int cls, char *ws, 
   const int32_t *list = c.Q.fast_task + 2 * (size_t)cls * (size_t)c.Q.fast_cap;
   for (;;) {
     __syncthreads();
-    if (threadIdx.x == 0) *s_base = atomicAdd(c.fast_next + cls, nwarps);
+    if (threadIdx.x == 0) *s_base = atomicAdd(c.ctl->fast_next + cls, nwarps);
     __syncthreads();
     const int base = *s_base;
     if (base >= nt) break;
@@ -275,7 +357,11 @@ __global__ void pack_kernel(const int64_t *__restrict__ offs, int n, OutBuf out,
                             const int64_t *__restrict__ struct_off, const int64_t *__restrict__ db_off,
                             const int64_t *__restrict__ step_off, const int64_t *__restrict__ ent_base,
                             int32_t *__restrict__ energy, char *__restrict__ db,
-                            int64_t *__restrict__ entry_off, int32_t *__restrict__ entry_struct) {
+                            int64_t *__restrict__ entry_off, int32_t *__restrict__ entry_struct,
+                            int64_t bS, int64_t bD, int64_t bT, int64_t bE, int64_t *__restrict__ g_off) {
+  /* bS/bD/bT/bE: what the lanes before this one hold (structures, dot-bracket bytes, steps, entries):
+   * the arrays written here are lane-local, the OFFSETS stored in them index the whole result;
+   * g_off = struct_off | db_off | step_off (n + 1 each) of this lane's sequences with the bases added */
   const int i = blockIdx.x;
   const int ns = out.seq_nstruct[i], nt = out.seq_nstep[i];
   const int64_t L = offs[i + 1] - offs[i];
@@ -293,10 +379,48 @@ __global__ void pack_kernel(const int64_t *__restrict__ offs, int n, OutBuf out,
   const int64_t ne = ent_base[i + 1] - e_dst;
   for (int64_t k = threadIdx.x; k < ne; k += blockDim.x) entry_struct[e_dst + k] = out.entries[e_src + k];
   if (threadIdx.x == 0) {
-    int64_t run = e_dst;
+    int64_t run = e_dst + bE;
     for (int s = 0; s < nt; s++) { entry_off[t_dst + s] = run; run += out.step_n[t_src + s]; }
     if (i == n - 1) entry_off[t_dst + nt] = run;
+    g_off[i] = s_dst + bS; g_off[(n + 1) + i] = d_dst + bD; g_off[2 * (n + 1) + i] = t_dst + bT;
+    if (i == n - 1) {
+      g_off[n] = struct_off[n] + bS; g_off[(n + 1) + n] = db_off[n] + bD; g_off[2 * (n + 1) + n] = step_off[n] + bT;
+    }
   }
+}
+
+/* INT32 issue-rate microbenchmark (rafft_int_peak): 8 independent chains per thread, IADD3 and LOP3
+ * alternating; every resident warp can issue every cycle, so the achieved warp-instructions per
+ * second are the issue-slot peak the fold kernels are measured against. */
+__global__ void __launch_bounds__(256) int_peak_kernel(unsigned *out, int iters, unsigned seed, int mode) {
+  unsigned a[8];
+#pragma unroll
+  for (int j = 0; j < 8; j++) a[j] = seed + threadIdx.x * 8 + j;
+  const unsigned b = seed * 3 + 1, c = seed ^ 0x55aa;
+  if (mode == 0) {
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+      for (int u = 0; u < 16; u++) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) asm volatile("add.u32 %0, %0, %1;" : "+r"(a[j]) : "r"(b));
+      }
+    }
+  } else {
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+      for (int u = 0; u < 16; u++) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          if (u & 1) asm volatile("add.u32 %0, %0, %1;" : "+r"(a[j]) : "r"(b));
+          else asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[j]) : "r"(b), "r"(c));
+        }
+      }
+    }
+  }
+  unsigned x = 0;
+#pragma unroll
+  for (int j = 0; j < 8; j++) x ^= a[j];
+  if (x == 0x12345678u) out[0] = x;
 }
 
 /* Whole-structure energy: one warp per structure.  Lane 0 builds the pair table with an
@@ -386,25 +510,65 @@ struct HostBlock {  /* pinned host memory handed out inside a rafft_result */
   size_t cap = 0;
 };
 
+#define RF_MAX_LANES 2      /* concurrent sub-batches per device */
+#define RF_MAX_DEVICES 16   /* contexts of one rafft_fold_batch_multi call */
+#define RF_GRAPH_SLOTS 4
+#define RF_PROF_EVENTS 12
+
+enum { FAM_GATHER = 0, FAM_EXPAND_FAST, FAM_EXPAND_GENERIC, FAM_COMBINE, FAM_SELECT, FAM_MATERIALISE,
+       FAM_ADVANCE, FAM_OTHER, FAM_N };
+
+/* the launch graph of one wave's fold (init -> WHILE{iteration} -> finish), cached by its kernel
+ * arguments: a repeated call with the same shapes re-launches the instantiated graph */
+struct GraphSlot {
+  cudaGraphExec_t exec = nullptr;
+  cudaGraph_t graph = nullptr;
+  std::vector<unsigned char> key;
+  uint64_t stamp = 0;
+};
+
+/* One lane = one stream with its own arenas, work lists, control block and output staging: an
+ * independent fold of a contiguous range of the batch.  A context runs up to RF_MAX_LANES lanes
+ * concurrently (lane 0 on a high-priority stream: it finishes first and its result copy overlaps
+ * the fold of lane 1). */
+struct Lane {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev1 = nullptr;
+  cudaEvent_t pev[RF_PROF_EVENTS] = {};
+  DevBuf arenas, order, idx, big, ordered, scan, states, tasks, ftasks, scratch, ctl, alist;
+  int64_t *h_small = nullptr;  /* pinned + mapped: [0..7] totals/cursors, [8..] loop progress words */
+  uint64_t arena_sig = 0;      /* layout of the arenas whose hash tables are known to be empty */
+  bool arena_dirty = true;
+  uint32_t seen_gen = 0;       /* generation of the last fold in the arenas (tag of its `seen` entries) */
+  size_t arena_clean = 0;      /* leading bytes of the arena buffer known to be clean */
+  GraphSlot graphs[RF_GRAPH_SLOTS];
+  uint64_t graph_clock = 0;
+  std::string err;
+};
+
 struct rafft_ctx {
   int device = 0;
   int sm_count = 148;
-  cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr, evx0 = nullptr, evx1 = nullptr;
+  cudaStream_t stream = nullptr;   /* = lane[0].stream (evaluator / kinetics entry points) */
+  cudaEvent_t ev_job = nullptr;
   DevEnergy *d_energy = nullptr;
-  DevBuf arenas, seqs, offs, order, idx, big, ordered, scan, evalbuf, states, tasks, ftasks, scratch, small, kinbuf;
+  Lane lane[RF_MAX_LANES];
+  DevBuf seqs, offs, evalbuf, kinbuf, peakbuf;
   std::vector<HostBlock> pinned_free;
-  int64_t *h_small = nullptr; /* pinned: totals + cursors */
+  std::mutex pin_mu;
   int block_threads = 64;   /* threads per block of the block-scope phase kernels */
   int blocks_per_sm = 16;   /* grid of the warp-task kernels: blocks per SM */
   int64_t max_wave = 0;     /* sequences folded together (0 = as many as memory allows) */
   int64_t max_tasks = 0;    /* capacity of the region work list (0 = automatic) */
   int fast_shape = 2;       /* index into g_fast_shapes (RAFFT_FAST_SHAPE) */
   int use_fast = 1;         /* shared-memory expansion for small regions (RAFFT_FAST=0 disables) */
-  uint64_t arena_sig = 0;   /* layout of the arenas whose hash tables are known to be empty */
-  bool arena_dirty = true;
-  uint32_t seen_gen = 0;    /* generation of the last fold in the arenas (tag of its `seen` entries) */
-  size_t arena_clean = 0;   /* leading bytes of the arena buffer known to be clean */
+  int loop_mode = 0;        /* 0 graph WHILE node, 1 stream launches with bounded look-ahead */
+  int lanes = 0;            /* 0 automatic, 1..RF_MAX_LANES forced */
+  int profile = 0;          /* per-kernel-family CUDA events (stepwise loop, one lane) */
+  int persist = 1;          /* blocks per SM of the persistent block-scope kernels = occupancy * persist */
+  int64_t mem_budget = 0;   /* bytes this context may use for arenas + scratch */
+  double traj_ratio = 5.0;  /* structures per (sequence x max_stack) of the last traj = 1 call */
+  uint32_t gen0 = 0;
   std::string err;
 };
 
@@ -424,11 +588,20 @@ static std::string g_create_err;
       return RAFFT_ERR_CUDA;                                                           \
     }                                                                                  \
   } while (0)
+/* the same inside a lane: the message goes to the lane (lanes run on their own host threads) */
+#define LCK(call)                                                                      \
+  do {                                                                                 \
+    cudaError_t e_ = (call);                                                           \
+    if (e_ != cudaSuccess) {                                                           \
+      ln.err = std::string(#call) + ": " + cudaGetErrorString(e_);                     \
+      return RAFFT_ERR_CUDA;                                                           \
+    }                                                                                  \
+  } while (0)
 
-static int dev_reserve(rafft_ctx *ctx, DevBuf &b, size_t bytes) {
+static int dev_reserve_s(std::string &err, DevBuf &b, size_t bytes) {
   if (bytes <= b.cap) return RAFFT_OK;
   if (getenv("RAFFT_DEBUG_ALLOC")) fprintf(stderr, "[rafft] cudaMalloc %zu bytes (had %zu)\n", bytes, b.cap);
-  if (b.p) { CK(cudaFree(b.p)); b.p = nullptr; b.cap = 0; }
+  if (b.p) { cudaFree(b.p); b.p = nullptr; b.cap = 0; }
   size_t want = bytes + bytes / 8 + 256;
   cudaError_t e = cudaMalloc(&b.p, want);
   if (e != cudaSuccess) {
@@ -438,14 +611,16 @@ static int dev_reserve(rafft_ctx *ctx, DevBuf &b, size_t bytes) {
   }
   if (e != cudaSuccess) {
     b.p = nullptr;
-    ctx->err = std::string("cudaMalloc(") + std::to_string(bytes) + "): " + cudaGetErrorString(e);
+    err = std::string("cudaMalloc(") + std::to_string(bytes) + "): " + cudaGetErrorString(e);
     return RAFFT_ERR_CUDA;
   }
   b.cap = want;
   return RAFFT_OK;
 }
+static int dev_reserve(rafft_ctx *ctx, DevBuf &b, size_t bytes) { return dev_reserve_s(ctx->err, b, bytes); }
 
 static int host_block_get(rafft_ctx *ctx, size_t bytes, HostBlock *hb) {
+  std::lock_guard<std::mutex> g(ctx->pin_mu);
   int best = -1;
   for (size_t k = 0; k < ctx->pinned_free.size(); k++)
     if (ctx->pinned_free[k].cap >= bytes && (best < 0 || ctx->pinned_free[k].cap < ctx->pinned_free[best].cap))
@@ -460,14 +635,31 @@ static int host_block_get(rafft_ctx *ctx, size_t bytes, HostBlock *hb) {
   ctx->pinned_free.clear();
   size_t want = bytes + bytes / 4 + 4096;
   if (getenv("RAFFT_DEBUG_ALLOC")) fprintf(stderr, "[rafft] cudaHostAlloc %zu bytes (request %zu)\n", want, bytes);
-  CK(cudaHostAlloc(&hb->p, want, cudaHostAllocDefault));
+  /* portable: the lanes of other devices copy straight into it (rafft_fold_batch_multi) */
+  CK(cudaHostAlloc(&hb->p, want, cudaHostAllocPortable));
   hb->cap = want;
   return RAFFT_OK;
 }
 
+static void lane_destroy(Lane &ln) {
+  DevBuf *bufs[] = {&ln.arenas, &ln.order, &ln.idx, &ln.big, &ln.ordered, &ln.scan, &ln.states,
+                    &ln.tasks, &ln.ftasks, &ln.scratch, &ln.ctl, &ln.alist};
+  for (DevBuf *b : bufs)
+    if (b->p) cudaFree(b->p);
+  for (GraphSlot &g : ln.graphs) {
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+    if (g.graph) cudaGraphDestroy(g.graph);
+  }
+  if (ln.h_small) cudaFreeHost(ln.h_small);
+  if (ln.ev1) cudaEventDestroy(ln.ev1);
+  for (cudaEvent_t e : ln.pev)
+    if (e) cudaEventDestroy(e);
+  if (ln.stream) cudaStreamDestroy(ln.stream);
+}
+
 extern "C" {
 
-const char *rafft_version(void) { return "rafft_b200 0.1 sm_100a"; }
+const char *rafft_version(void) { return "rafft_b200 0.2 sm_100a"; }
 
 void rafft_default_energy_params(rafft_energy_params *ep) {
   if (ep) default_energy_params(ep);
@@ -478,19 +670,13 @@ const char *rafft_last_error(const rafft_ctx *ctx) { return ctx ? ctx->err.c_str
 void rafft_destroy(rafft_ctx *ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
-  DevBuf *bufs[] = {&ctx->arenas, &ctx->seqs, &ctx->offs, &ctx->order, &ctx->idx,
-                    &ctx->states, &ctx->tasks, &ctx->ftasks, &ctx->scratch, &ctx->small,
-                    &ctx->big, &ctx->ordered, &ctx->scan, &ctx->evalbuf, &ctx->kinbuf};
+  for (Lane &ln : ctx->lane) lane_destroy(ln);
+  DevBuf *bufs[] = {&ctx->seqs, &ctx->offs, &ctx->evalbuf, &ctx->kinbuf, &ctx->peakbuf};
   for (DevBuf *b : bufs)
     if (b->p) cudaFree(b->p);
   for (auto &b : ctx->pinned_free) cudaFreeHost(b.p);
-  if (ctx->h_small) cudaFreeHost(ctx->h_small);
   if (ctx->d_energy) cudaFree(ctx->d_energy);
-  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
-  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
-  if (ctx->evx0) cudaEventDestroy(ctx->evx0);
-  if (ctx->evx1) cudaEventDestroy(ctx->evx1);
-  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  if (ctx->ev_job) cudaEventDestroy(ctx->ev_job);
   delete ctx;
 }
 
@@ -527,18 +713,27 @@ int rafft_create(rafft_ctx **out, int cuda_device, const rafft_energy_params *ep
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, cuda_device));
     ctx->sm_count = prop.multiProcessorCount;
-    CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-    CK(cudaEventCreate(&ctx->ev0));
-    CK(cudaEventCreate(&ctx->ev1));
-    CK(cudaEventCreate(&ctx->evx0));
-    CK(cudaEventCreate(&ctx->evx1));
+    int prio_lo = 0, prio_hi = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi)); /* numerically lower = higher priority */
+    for (int k = 0; k < RF_MAX_LANES; k++) {
+      Lane &ln = ctx->lane[k];
+      CK(cudaStreamCreateWithPriority(&ln.stream, cudaStreamNonBlocking, k == 0 ? prio_hi : prio_lo));
+      CK(cudaEventCreate(&ln.ev1));
+      for (cudaEvent_t &pe : ln.pev) CK(cudaEventCreate(&pe));
+      CK(cudaHostAlloc((void **)&ln.h_small, 64 * sizeof(int64_t), cudaHostAllocMapped | cudaHostAllocPortable));
+      memset(ln.h_small, 0, 64 * sizeof(int64_t));
+    }
+    ctx->stream = ctx->lane[0].stream;
+    CK(cudaEventCreate(&ctx->ev_job));
     CK(cudaMalloc((void **)&ctx->d_energy, sizeof(DevEnergy)));
     CK(cudaMemcpy(ctx->d_energy, D, sizeof(DevEnergy), cudaMemcpyHostToDevice));
-    CK(cudaHostAlloc((void **)&ctx->h_small, 64 * sizeof(int64_t), cudaHostAllocDefault));
+    size_t free_b = 0, total_b = 0;
+    CK(cudaMemGetInfo(&free_b, &total_b));
+    ctx->mem_budget = (int64_t)(free_b * 0.7);
     const char *s = getenv("RAFFT_BLOCK_THREADS");
     if (s) { int v = atoi(s); if (v >= 32 && v <= RF_BLOCK_THREADS_MAX && v % 32 == 0) ctx->block_threads = v; }
     s = getenv("RAFFT_SEEN_GEN0"); /* tests: start near the wrap of the `seen` generation counter */
-    if (s) { int v = atoi(s); if (v >= 0 && v <= 65535) ctx->seen_gen = (uint32_t)v; }
+    if (s) { int v = atoi(s); if (v >= 0 && v <= 65535) for (Lane &ln : ctx->lane) ln.seen_gen = (uint32_t)v; }
     s = getenv("RAFFT_BLOCKS_PER_SM");
     if (s) { int v = atoi(s); if (v >= 1 && v <= 32) ctx->blocks_per_sm = v; }
     s = getenv("RAFFT_MAX_WAVE");
@@ -549,6 +744,14 @@ int rafft_create(rafft_ctx **out, int cuda_device, const rafft_energy_params *ep
     if (s) ctx->use_fast = atoi(s) != 0;
     s = getenv("RAFFT_MAX_TASKS");
     if (s) { long v = atol(s); if (v >= 1) ctx->max_tasks = v; }
+    s = getenv("RAFFT_LOOP"); /* graph (default) | stream */
+    if (s) ctx->loop_mode = strcmp(s, "stream") == 0 ? 1 : 0;
+    s = getenv("RAFFT_LANES");
+    if (s) { int v = atoi(s); if (v >= 0 && v <= RF_MAX_LANES) ctx->lanes = v; }
+    s = getenv("RAFFT_PROFILE");
+    if (s) ctx->profile = atoi(s) != 0;
+    s = getenv("RAFFT_PERSIST");
+    if (s) { int v = atoi(s); if (v >= 1 && v <= 8) ctx->persist = v; }
     return RAFFT_OK;
   }();
   free(D);
@@ -561,16 +764,31 @@ int rafft_create(rafft_ctx **out, int cuda_device, const rafft_energy_params *ep
   return RAFFT_OK;
 }
 
+int rafft_set_option(rafft_ctx *ctx, const char *name, int64_t value) {
+  if (!ctx || !name) return RAFFT_ERR_ARG;
+  std::string k(name);
+  if (k == "profile") ctx->profile = value != 0;
+  else if (k == "lanes" && value >= 0 && value <= RF_MAX_LANES) ctx->lanes = (int)value;
+  else if (k == "loop" && (value == 0 || value == 1)) ctx->loop_mode = (int)value;
+  else if (k == "max_wave" && value >= 0) ctx->max_wave = value;
+  else if (k == "persist" && value >= 1 && value <= 8) ctx->persist = (int)value;
+  else { ctx->err = "rafft_set_option: unknown option or value out of range: " + k; return RAFFT_ERR_ARG; }
+  return RAFFT_OK;
+}
+
 void rafft_result_free(rafft_result *res) {
   if (!res) return;
   ResultImpl *r = (ResultImpl *)res;
-  if (r->block.p) r->ctx->pinned_free.push_back(r->block);
+  if (r->block.p) {
+    std::lock_guard<std::mutex> g(r->ctx->pin_mu);
+    r->ctx->pinned_free.push_back(r->block);
+  }
   delete r;
 }
 
 }  // extern "C"
 
-/* Layout of the index part of OutBuf inside ctx->idx for n sequences. */
+/* Layout of the index part of OutBuf inside Lane::idx for n sequences. */
 static size_t idx_layout(OutBuf &o, char *base, int n) {
   size_t off = 0;
   auto carve = [&](size_t bytes) { off = align_up(off, 16); char *p = base ? base + off : nullptr; off += bytes; return p; };
@@ -596,75 +814,248 @@ static size_t big_layout(OutBuf &o, char *base) {
   return align_up(off, 256);
 }
 
-/* The fold proper, inputs on the device.  h_offs: host copy of the offsets (n+1). */
-static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs, const int64_t *h_offs,
-                       int32_t n, const rafft_params *params, rafft_result **out_res,
-                       int64_t h2d_bytes) {
-  std::string err;
-  const bool dbg = getenv("RAFFT_DEBUG_ALLOC") != nullptr;
-  auto t_start = std::chrono::steady_clock::now();
-  auto lap = [&](const char *what) {
-    if (dbg) fprintf(stderr, "[rafft] %-18s +%.2f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count());
-  };
+/* ---- one call = one job; its lanes (streams, possibly on several devices) fold contiguous ranges
+ * of the batch and copy their part of the result into ONE pinned host block -------------------- */
+struct LaneTask {
+  rafft_ctx *ctx = nullptr;
+  int lane = 0;          /* lane of ctx */
+  int i0 = 0, i1 = 0;    /* its sequences [i0, i1) of the job */
+  const char *d_seqs = nullptr;
+  const int64_t *d_offs = nullptr; /* n + 1 offsets of the whole job on this lane's device */
+  int first_of_ctx = 0;  /* records / owns ev_job of its context */
+  /* results */
+  int rc = RAFFT_OK;
+  int64_t totals[4] = {0, 0, 0, 0};
+  int64_t launches = 0, d2h = 0, h2d = 0, iters = 0;
+  float span_ms = 0.f;   /* ev_job -> end of this lane's pack */
+  double fam_ms[FAM_N] = {0, 0, 0, 0, 0, 0, 0, 0};
+  int64_t fam_n[FAM_N] = {0, 0, 0, 0, 0, 0, 0, 0};
+  std::vector<int32_t> h_status;
+  bool copied = false;   /* its sections are in the job's host block */
+  int waves = 0;
+  OutBuf O;              /* device output of the fold (between the two halves of the lane) */
+};
+
+struct FoldJob {
+  int n = 0;
+  const int64_t *h_offs = nullptr;
+  const rafft_params *params = nullptr;
   FoldParams F;
-  if (!build_fold_params(params, &F, err)) { ctx->err = "rafft_fold_batch: " + err; return RAFFT_ERR_ARG; }
-  int L_max = 1;
-  int64_t total_len = h_offs[n] - h_offs[0];
-  for (int i = 0; i < n; i++) {
-    int64_t L = h_offs[i + 1] - h_offs[i];
-    if (L < 0 || L > 4096) {
-      ctx->err = "rafft_fold_batch: sequence length must be in [0, 4096]";
-      return RAFFT_ERR_ARG;
-    }
-    if (L > L_max) L_max = (int)L;
+  std::vector<LaneTask> lanes;
+  std::mutex mu;
+  std::condition_variable cv;
+  int published = 0;                 /* lanes 0 .. published-1 have added their totals to cum */
+  int64_t cum[RF_MAX_LANES * RF_MAX_DEVICES + 1][4];
+  bool abort = false;
+  /* host block: energy | entry_struct | entry_off | db | status | struct_off | db_off | step_off | counters */
+  HostBlock block;
+  int64_t cap[4] = {0, 0, 0, 0};     /* capacities of the four data sections (structures, db bytes, steps, entries) */
+  size_t o_energy = 0, o_entry = 0, o_entoff = 0, o_db = 0, o_status = 0, o_soff = 0, o_doff = 0, o_toff = 0, o_cnt = 0, o_end = 0;
+  bool overflow = false;
+};
+
+static void job_layout(FoldJob &J) {
+  const size_t n = (size_t)J.n;
+  J.o_energy = 0;
+  J.o_entry = align_up(J.o_energy + sizeof(int32_t) * (size_t)J.cap[0], 256);
+  J.o_entoff = align_up(J.o_entry + sizeof(int32_t) * (size_t)J.cap[3], 256);
+  J.o_db = align_up(J.o_entoff + sizeof(int64_t) * (size_t)(J.cap[2] + 1), 256);
+  J.o_status = align_up(J.o_db + (size_t)J.cap[1], 256);
+  J.o_soff = align_up(J.o_status + sizeof(int32_t) * n, 16);
+  J.o_doff = J.o_soff + sizeof(int64_t) * (n + 1);
+  J.o_toff = J.o_doff + sizeof(int64_t) * (n + 1);
+  J.o_cnt = J.o_toff + sizeof(int64_t) * (n + 1);
+  J.o_end = J.o_cnt + sizeof(int64_t) * n * CNT_N + 64;
+}
+
+/* kernel launch either on a stream or as a node of a graph (same arguments) */
+struct Emit {
+  cudaStream_t stream = nullptr;
+  cudaGraph_t graph = nullptr;
+  cudaGraphNode_t prev = nullptr;
+  bool have_prev = false;
+  cudaError_t err = cudaSuccess;
+  void kernel(const void *fn, dim3 grid, dim3 block, size_t smem, void **args) {
+    if (err != cudaSuccess) return;
+    if (!graph) { err = cudaLaunchKernel(fn, grid, block, args, smem, stream); return; }
+    cudaKernelNodeParams kp;
+    memset(&kp, 0, sizeof kp);
+    kp.func = (void *)fn; kp.gridDim = grid; kp.blockDim = block; kp.sharedMemBytes = (unsigned)smem;
+    kp.kernelParams = args; kp.extra = nullptr;
+    cudaGraphNode_t node;
+    err = cudaGraphAddKernelNode(&node, graph, have_prev ? &prev : nullptr, have_prev ? 1 : 0, &kp);
+    prev = node; have_prev = true;
   }
-  const int T = ctx->block_threads;
-  /* per-kernel overrides of the block size (tuning; same results for any value) */
+};
+
+/* launch shape of one wave's fold */
+struct WavePlan {
+  WaveCtx wc;
+  int nw = 0;
+  int T = 64, T_gather = 64, T_combine = 128, T_select = 64, T_mat = 64, T_finish = 256;
+  int g_gather = 0, g_combine = 0, g_select = 0, g_mat = 0, g_fast = 0, egrid = 0;
+  size_t stage_bytes = 0, fast_smem = 0;
+  const FastShape *fsh = nullptr;
+  bool use_fast = false, any_generic = false;
+};
+
+/* the kernels of one folding iteration; fam_ev != nullptr: a CUDA event before every kernel family
+ * (profile mode, stream only) */
+static void emit_iteration(Emit &E, WavePlan &P, cudaGraphConditionalHandle handle, int use_handle,
+                           cudaEvent_t *fam_ev) {
+  WaveCtx &wc = P.wc;
+  void *a_wc[] = {&wc};
+  int ne = 0;
+  auto mark = [&]() { if (fam_ev && E.err == cudaSuccess) E.err = cudaEventRecord(fam_ev[ne++], E.stream); };
+  mark();
+  E.kernel((const void *)k_gather, dim3(P.g_gather), dim3(P.T_gather), 0, a_wc);
+  mark();
+  if (P.use_fast) E.kernel((const void *)P.fsh->fn, dim3(P.g_fast), dim3(P.fsh->threads), P.fast_smem, a_wc);
+  mark();
+  if (P.any_generic) {
+    E.kernel((const void *)k_expand<1>, dim3(P.egrid), dim3(128), 0, a_wc);
+    E.kernel((const void *)k_expand<2>, dim3(P.egrid), dim3(128), 0, a_wc);
+    E.kernel((const void *)k_expand<3>, dim3(P.egrid), dim3(128), 0, a_wc);
+    E.kernel((const void *)k_expand<4>, dim3(P.egrid), dim3(128), 0, a_wc);
+    E.kernel((const void *)k_expand<5>, dim3(P.egrid), dim3(128), 0, a_wc);
+  }
+  mark();
+  E.kernel((const void *)k_combine, dim3(P.g_combine), dim3(P.T_combine), P.stage_bytes, a_wc);
+  mark();
+  E.kernel((const void *)k_select, dim3(P.g_select), dim3(P.T_select), (size_t)wc.sel_smem, a_wc);
+  mark();
+  E.kernel((const void *)k_materialise, dim3(P.g_mat), dim3(P.T_mat), 0, a_wc);
+  mark();
+  LoopCtl *ctl = wc.ctl;
+  int32_t *hp = wc.h_prog;
+  void *a_adv[] = {&ctl, &hp, &handle, &use_handle};
+  E.kernel((const void *)k_advance, dim3(1), dim3(32), 0, a_adv);
+  mark();
+}
+
+/* Graph of one wave's fold: k_init -> WHILE { iteration } -> k_finish.  Returns nullptr (and leaves
+ * `why`) when the graph cannot be built; the caller then drives the same kernels from the stream. */
+static cudaGraphExec_t wave_graph(Lane &ln, WavePlan &P, std::string &why) {
+  /* key: every kernel argument and launch dimension */
+  std::vector<unsigned char> key(sizeof(WaveCtx) + 16 * sizeof(int) + 2 * sizeof(size_t));
+  {
+    unsigned char *k = key.data();
+    memcpy(k, &P.wc, sizeof(WaveCtx)); k += sizeof(WaveCtx);
+    const int dims[16] = {P.nw, P.T, P.T_gather, P.T_combine, P.T_select, P.T_mat, P.T_finish, P.g_gather,
+                          P.g_combine, P.g_select, P.g_mat, P.g_fast, P.egrid, P.use_fast, P.any_generic,
+                          P.fsh ? P.fsh->threads : 0};
+    memcpy(k, dims, sizeof dims); k += sizeof dims;
+    memcpy(k, &P.stage_bytes, sizeof(size_t)); k += sizeof(size_t);
+    memcpy(k, &P.fast_smem, sizeof(size_t));
+  }
+  GraphSlot *victim = &ln.graphs[0];
+  for (GraphSlot &g : ln.graphs) {
+    if (g.exec && g.key == key) { g.stamp = ++ln.graph_clock; return g.exec; }
+    if (g.stamp < victim->stamp) victim = &g;
+  }
+  if (victim->exec) { cudaGraphExecDestroy(victim->exec); victim->exec = nullptr; }
+  if (victim->graph) { cudaGraphDestroy(victim->graph); victim->graph = nullptr; }
+  victim->key.clear();
+  cudaGraph_t g = nullptr;
+  auto fail = [&](const char *what, cudaError_t e) {
+    why = std::string(what) + ": " + cudaGetErrorString(e);
+    (void)cudaGetLastError();
+    if (g) cudaGraphDestroy(g);
+    return (cudaGraphExec_t) nullptr;
+  };
+  cudaError_t e = cudaGraphCreate(&g, 0);
+  if (e != cudaSuccess) return fail("cudaGraphCreate", e);
+  Emit top;
+  top.graph = g;
+  void *a_wc[] = {&P.wc};
+  top.kernel((const void *)k_init, dim3(P.nw), dim3(P.T), 0, a_wc);
+  if (top.err != cudaSuccess) return fail("k_init node", top.err);
+  cudaGraphConditionalHandle handle;
+  e = cudaGraphConditionalHandleCreate(&handle, g, 1, cudaGraphCondAssignDefault);
+  if (e != cudaSuccess) return fail("cudaGraphConditionalHandleCreate", e);
+  cudaGraphNodeParams cp = {};
+  cp.type = cudaGraphNodeTypeConditional;
+  cp.conditional.handle = handle;
+  cp.conditional.type = cudaGraphCondTypeWhile;
+  cp.conditional.size = 1;
+  cudaGraphNode_t wnode;
+  e = cudaGraphAddNode(&wnode, g, &top.prev, 1, &cp);
+  if (e != cudaSuccess) return fail("conditional WHILE node", e);
+  Emit body;
+  body.graph = cp.conditional.phGraph_out[0];
+  emit_iteration(body, P, handle, 1, nullptr);
+  if (body.err != cudaSuccess) return fail("iteration nodes", body.err);
+  top.prev = wnode;
+  top.kernel((const void *)k_finish, dim3(P.nw), dim3(P.T_finish), 0, a_wc);
+  if (top.err != cudaSuccess) return fail("k_finish node", top.err);
+  cudaGraphExec_t exec = nullptr;
+  e = cudaGraphInstantiate(&exec, g, 0);
+  if (e != cudaSuccess) return fail("cudaGraphInstantiate", e);
+  victim->exec = exec; victim->graph = g; victim->key = key; victim->stamp = ++ln.graph_clock;
+  return exec;
+}
+
+/* Fold the sequences [i0, i1) of the job on one lane and copy its part of the result into the
+ * job's host block.  Runs on its own host thread when the job has several lanes. */
+static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to the totals of its result */
+  LaneTask &T = J.lanes[(size_t)k];
+  rafft_ctx *ctx = T.ctx;
+  Lane &ln = ctx->lane[T.lane];
+  const FoldParams &F = J.F;
+  const int m_all = T.i1 - T.i0;
+  const int64_t *h_offs = J.h_offs + T.i0;   /* offsets of this lane's sequences */
+  const int64_t *d_offs = T.d_offs + T.i0;
+  const bool dbg = getenv("RAFFT_DEBUG_ALLOC") != nullptr;
+  const bool profile = ctx->profile != 0;
+  LCK(cudaSetDevice(ctx->device));
+  LCK(cudaStreamWaitEvent(ln.stream, ctx->ev_job, 0));
+  int L_max = 1;
+  int64_t total_len = h_offs[m_all] - h_offs[0];
+  for (int i = 0; i < m_all; i++) L_max = std::max<int64_t>(L_max, h_offs[i + 1] - h_offs[i]);
+  const int Tb = ctx->block_threads;
   auto threads_of = [&](const char *name, int dflt) {
     const char *e = getenv(name);
     const int v = e ? atoi(e) : 0;
     return (v >= 32 && v <= RF_BLOCK_THREADS_MAX && v % 32 == 0) ? v : dflt;
   };
+  WavePlan P;
+  P.T = Tb;
   /* measured on B200 (tools/threads_sweep.sh): the product enumeration wants 4 warps per sequence
    * (more look-ups in flight), selection and materialisation 2 warps up to -ms 100 and 4 beyond */
-  const int T_ms = params->max_stack > 100 && T == 64 ? 128 : T;
-  const int T_gather = threads_of("RAFFT_GATHER_THREADS", T), T_combine = threads_of("RAFFT_COMBINE_THREADS", T == 64 ? 128 : T);
-  const int T_select = threads_of("RAFFT_SELECT_THREADS", T_ms), T_mat = threads_of("RAFFT_MATERIALISE_THREADS", T_ms);
-  const int T_finish = threads_of("RAFFT_FINISH_THREADS", RF_BLOCK_THREADS_MAX);
-  ResultImpl *R = new ResultImpl;
-  memset(&R->pub, 0, sizeof R->pub);
-  R->ctx = ctx;
-  R->block = HostBlock();
-  auto fail = [&](int rc) { rafft_result_free(&R->pub); return rc; };
-  int64_t launches = 0, d2h = 0;
-  float kernel_ms = 0.f;
-  double expand_ms = 0.0;
-  int64_t expand_launches = 0;
+  const int T_ms = J.params->max_stack > 100 && Tb == 64 ? 128 : Tb;
+  P.T_gather = threads_of("RAFFT_GATHER_THREADS", Tb);
+  P.T_combine = threads_of("RAFFT_COMBINE_THREADS", Tb == 64 ? 128 : Tb);
+  P.T_select = threads_of("RAFFT_SELECT_THREADS", T_ms);
+  P.T_mat = threads_of("RAFFT_MATERIALISE_THREADS", T_ms);
+  P.T_finish = threads_of("RAFFT_FINISH_THREADS", RF_BLOCK_THREADS_MAX);
 
   /* index part of the output */
   OutBuf O;
   memset(&O, 0, sizeof O);
-  size_t idx_bytes = idx_layout(O, nullptr, n);
-  if (int rc = dev_reserve(ctx, ctx->idx, idx_bytes)) return fail(rc);
-  idx_layout(O, (char *)ctx->idx.p, n);
-  if (cudaMemsetAsync(ctx->idx.p, 0, idx_bytes, ctx->stream) != cudaSuccess) { ctx->err = "memset"; return fail(RAFFT_ERR_CUDA); }
-  if (int rc = dev_reserve(ctx, ctx->order, sizeof(int32_t) * (size_t)(n + 1))) return fail(rc);
+  const size_t idx_bytes = idx_layout(O, nullptr, m_all);
+  if (int rc = dev_reserve_s(ln.err, ln.idx, idx_bytes)) return rc;
+  idx_layout(O, (char *)ln.idx.p, m_all);
+  LCK(cudaMemsetAsync(ln.idx.p, 0, idx_bytes, ln.stream));
+  if (int rc = dev_reserve_s(ln.err, ln.order, sizeof(int32_t) * (size_t)(m_all + 1))) return rc;
+  if (int rc = dev_reserve_s(ln.err, ln.ctl, sizeof(LoopCtl))) return rc;
+  int32_t *h_prog = (int32_t *)(ln.h_small + 8);
 
-  std::vector<int32_t> todo;          /* sequences still to fold (empty = all) */
-  std::vector<int32_t> h_status(n > 0 ? n : 1), h_order;
+  std::vector<int32_t> todo, h_order;
+  T.h_status.assign((size_t)(m_all > 0 ? m_all : 1), 0);
   int scale = 1;
-  int64_t used[4] = {0, 0, 0, 0};      /* cursors after the previous round */
-  for (int round = 0; n > 0; round++) {
-    const int m = round == 0 ? n : (int)todo.size();
+  int64_t used[4] = {0, 0, 0, 0};
+  const int n_lanes_ctx = std::max(1, (int)std::count_if(J.lanes.begin(), J.lanes.end(), [&](const LaneTask &t) { return t.ctx == ctx; }));
+  for (int round = 0; m_all > 0; round++) {
+    const int m = round == 0 ? m_all : (int)todo.size();
     int Lr = L_max;
     if (round > 0) {
       Lr = 1;
       for (int i : todo) Lr = std::max<int64_t>(Lr, h_offs[i + 1] - h_offs[i]);
     }
-    Caps caps = make_caps(Lr, F, T, scale);
+    Caps caps = make_caps(Lr, F, Tb, scale);
     /* output capacities for this round (bump-allocated after what is already used) */
-    int64_t per_struct = F.traj ? caps.store_cap : F.max_stack;
-    int64_t per_step = F.traj ? caps.step_cap : 1;
+    const int64_t per_struct = F.traj ? caps.store_cap : F.max_stack;
+    const int64_t per_step = F.traj ? caps.step_cap : 1;
     int64_t sum_L = 0;
     if (round == 0) sum_L = total_len;
     else for (int i : todo) sum_L += h_offs[i + 1] - h_offs[i];
@@ -673,27 +1064,26 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     N.db_cap = used[1] + per_struct * (sum_L + 15 * (int64_t)m); /* rows padded to 16 bytes */
     N.step_cap = used[2] + per_step * m;
     N.entry_cap = used[3] + (F.traj ? per_step * F.max_stack : (int64_t)F.max_stack) * m;
-    size_t big_bytes = big_layout(N, nullptr);
+    const size_t big_bytes = big_layout(N, nullptr);
     if (round == 0) {
-      if (int rc = dev_reserve(ctx, ctx->big, big_bytes)) return fail(rc);
-      big_layout(N, (char *)ctx->big.p);
+      if (int rc = dev_reserve_s(ln.err, ln.big, big_bytes)) return rc;
+      big_layout(N, (char *)ln.big.p);
     } else {
       DevBuf nb;
-      if (int rc = dev_reserve(ctx, nb, big_bytes)) return fail(rc);
+      if (int rc = dev_reserve_s(ln.err, nb, big_bytes)) return rc;
       big_layout(N, (char *)nb.p);
-      cudaMemcpyAsync(N.energy, O.energy, sizeof(int32_t) * (size_t)used[0], cudaMemcpyDeviceToDevice, ctx->stream);
-      cudaMemcpyAsync(N.db, O.db, (size_t)used[1], cudaMemcpyDeviceToDevice, ctx->stream);
-      cudaMemcpyAsync(N.step_n, O.step_n, sizeof(int32_t) * (size_t)used[2], cudaMemcpyDeviceToDevice, ctx->stream);
-      cudaMemcpyAsync(N.entries, O.entries, sizeof(int32_t) * (size_t)used[3], cudaMemcpyDeviceToDevice, ctx->stream);
-      CK(cudaStreamSynchronize(ctx->stream));
-      cudaFree(ctx->big.p);
-      ctx->big = nb;
+      cudaMemcpyAsync(N.energy, O.energy, sizeof(int32_t) * (size_t)used[0], cudaMemcpyDeviceToDevice, ln.stream);
+      cudaMemcpyAsync(N.db, O.db, (size_t)used[1], cudaMemcpyDeviceToDevice, ln.stream);
+      cudaMemcpyAsync(N.step_n, O.step_n, sizeof(int32_t) * (size_t)used[2], cudaMemcpyDeviceToDevice, ln.stream);
+      cudaMemcpyAsync(N.entries, O.entries, sizeof(int32_t) * (size_t)used[3], cudaMemcpyDeviceToDevice, ln.stream);
+      const cudaError_t se = cudaStreamSynchronize(ln.stream);
+      cudaFree(ln.big.p);
+      ln.big = nb; /* the lane owns the new buffer from here on (freed with the lane) */
+      if (se != cudaSuccess) { ln.err = std::string("result regrowth: ") + cudaGetErrorString(se); return RAFFT_ERR_CUDA; }
     }
     O = N;
     /* waves: as many sequences at once as the memory budget allows (one arena each) */
-    size_t free_b = 0, total_b = 0;
-    CK(cudaMemGetInfo(&free_b, &total_b));
-    int64_t budget = (int64_t)((free_b + ctx->arenas.cap + ctx->scratch.cap) * 0.7);
+    const int64_t budget = ctx->mem_budget / n_lanes_ctx;
     int64_t wave = std::min<int64_t>(m, std::max<int64_t>(1, (budget * 3 / 4) / caps.arena_bytes));
     if (ctx->max_wave > 0) wave = std::min<int64_t>(wave, ctx->max_wave);
     int64_t qcap = std::min<int64_t>(wave * 64, std::max<int64_t>(64, (budget / 4) / caps.wscratch_bytes));
@@ -709,230 +1099,477 @@ static int fold_device(rafft_ctx *ctx, const char *d_seqs, const int64_t *d_offs
     }
     if (ctx->max_tasks > 0) { qcap = std::min<int64_t>(qcap, ctx->max_tasks); fcap = std::min<int64_t>(fcap, ctx->max_tasks); }
     {
-      /* The hash tables at the head of every arena must be empty before a run; a run leaves
-       * them empty again, so they are zeroed only when the buffer or its layout changes. */
-      void *before = ctx->arenas.p;
-      if (int rc = dev_reserve(ctx, ctx->arenas, (size_t)(wave * caps.arena_bytes))) return fail(rc);
+      /* The unique-loop tables at the head of every arena must be empty before a run; a run leaves
+       * them empty again, so they are zeroed only when the buffer or its layout changes (or after
+       * a failed call: arena_dirty). */
+      void *before = ln.arenas.p;
+      if (int rc = dev_reserve_s(ln.err, ln.arenas, (size_t)(wave * caps.arena_bytes))) return rc;
       uint64_t sig = 1469598103934665603ULL;
       const unsigned char *cb = (const unsigned char *)&caps;
-      for (size_t k = 0; k < sizeof caps; k++) sig = (sig ^ cb[k]) * 1099511628211ULL;
+      for (size_t q = 0; q < sizeof caps; q++) sig = (sig ^ cb[q]) * 1099511628211ULL;
       const size_t need = (size_t)(wave * caps.arena_bytes);
-      if (before != ctx->arenas.p || sig != ctx->arena_sig || ctx->arena_dirty) {
-        CK(cudaMemsetAsync(ctx->arenas.p, 0, need, ctx->stream));
-        ctx->arena_sig = sig;
-        ctx->arena_dirty = false;
-        ctx->arena_clean = need;
-      } else if (need > ctx->arena_clean) {
-        CK(cudaMemsetAsync((char *)ctx->arenas.p + ctx->arena_clean, 0, need - ctx->arena_clean, ctx->stream));
-        ctx->arena_clean = need;
+      if (before != ln.arenas.p || sig != ln.arena_sig || ln.arena_dirty) {
+        LCK(cudaMemsetAsync(ln.arenas.p, 0, need, ln.stream));
+        ln.arena_sig = sig;
+        ln.arena_clean = need;
+      } else if (need > ln.arena_clean) {
+        LCK(cudaMemsetAsync((char *)ln.arenas.p + ln.arena_clean, 0, need - ln.arena_clean, ln.stream));
+        ln.arena_clean = need;
       }
+      ln.arena_dirty = true; /* until this fold has run to its end */
     }
-    if (int rc = dev_reserve(ctx, ctx->states, sizeof(SeqState) * (size_t)wave)) return fail(rc);
-    if (int rc = dev_reserve(ctx, ctx->tasks, sizeof(int32_t) * 2 * (size_t)qcap)) return fail(rc);
-    if (int rc = dev_reserve(ctx, ctx->ftasks, sizeof(int32_t) * 2 * RF_FAST_LISTS * (size_t)(fcap + 1))) return fail(rc);
-    if (int rc = dev_reserve(ctx, ctx->scratch, (size_t)qcap * (size_t)caps.wscratch_bytes)) return fail(rc);
-    if (int rc = dev_reserve(ctx, ctx->small, 256)) return fail(rc);
-    WaveCtx wc;
+    if (int rc = dev_reserve_s(ln.err, ln.states, sizeof(SeqState) * (size_t)wave)) return rc;
+    if (int rc = dev_reserve_s(ln.err, ln.tasks, sizeof(int32_t) * 2 * (size_t)qcap)) return rc;
+    if (int rc = dev_reserve_s(ln.err, ln.ftasks, sizeof(int32_t) * 2 * RF_FAST_LISTS * (size_t)(fcap + 1))) return rc;
+    if (int rc = dev_reserve_s(ln.err, ln.scratch, (size_t)qcap * (size_t)caps.wscratch_bytes)) return rc;
+    if (int rc = dev_reserve_s(ln.err, ln.alist, sizeof(int32_t) * 2 * (size_t)wave)) return rc;
+    WaveCtx &wc = P.wc;
     memset(&wc, 0, sizeof wc);
     wc.E = ctx->d_energy; wc.prm = F; wc.caps = caps;
     arena_offsets(wc.aoff, caps, F);
-    wc.arenas = (char *)ctx->arenas.p; wc.states = (SeqState *)ctx->states.p;
-    wc.seqs = d_seqs; wc.offs = d_offs;
-    wc.Q.n_tasks = (int32_t *)ctx->small.p; wc.Q.cap = (int32_t)qcap; wc.Q.task = (int32_t *)ctx->tasks.p;
-    wc.Q.scratch = (char *)ctx->scratch.p; wc.Q.self = 0;
-    wc.n_active = (int32_t *)ctx->small.p + 1;
-    wc.Q.n_fast = (int32_t *)ctx->small.p + 2; wc.Q.fast_cap = (int32_t)fcap; wc.Q.fast_task = (int32_t *)ctx->ftasks.p;
+    wc.arenas = (char *)ln.arenas.p; wc.states = (SeqState *)ln.states.p;
+    wc.seqs = T.d_seqs; wc.offs = d_offs;
+    LoopCtl *ctl = (LoopCtl *)ln.ctl.p;
+    wc.ctl = ctl;
+    wc.alist = (int32_t *)ln.alist.p; wc.acap = (int32_t)wave;
+    wc.h_prog = h_prog;
+    wc.Q.n_tasks = &ctl->n_tasks; wc.Q.cap = (int32_t)qcap; wc.Q.task = (int32_t *)ln.tasks.p;
+    wc.Q.scratch = (char *)ln.scratch.p; wc.Q.self = 0;
+    wc.Q.n_fast = ctl->n_fast; wc.Q.fast_cap = (int32_t)fcap; wc.Q.fast_task = (int32_t *)ln.ftasks.p;
     wc.Q.fast_lv = fastcfg.L_cap; wc.Q.fast_br = fastcfg.br_cap;
     wc.fast = fastcfg;
-    wc.fast_next = (int32_t *)ctx->small.p + 2 + RF_FAST_LISTS;
-    const FastShape &fsh = g_fast_shapes[ctx->fast_shape];
-    const size_t fast_smem = (size_t)(fsh.threads / 32) * (size_t)fastcfg.smem_per_warp;
+    P.fsh = &g_fast_shapes[ctx->fast_shape];
+    P.fast_smem = (size_t)(P.fsh->threads / 32) * (size_t)fastcfg.smem_per_warp;
+    P.use_fast = fcap > 0;
     /* a branch of a loop covers at least min_hp + 2 positions */
-    const bool any_generic = fcap == 0 || Lr > fastcfg.L_cap || Lr / (F.min_hp + 2) > fastcfg.br_cap;
+    P.any_generic = fcap == 0 || Lr > fastcfg.L_cap || Lr / (F.min_hp + 2) > fastcfg.br_cap;
     wc.out = O;
     CombineStage cs_probe;
-    const size_t stage_bytes = stage_carve(cs_probe, nullptr, caps.chunk_cap, F.max_stack);
-    CK(cudaFuncSetAttribute(k_combine, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stage_bytes));
+    P.stage_bytes = stage_carve(cs_probe, nullptr, caps.chunk_cap, F.max_stack);
+    LCK(cudaFuncSetAttribute(k_combine, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P.stage_bytes));
     {
       const size_t sel_bytes = sizeof(int32_t) * (size_t)std::max<int64_t>(caps.chunk_cap, (int64_t)caps.new_cap + F.max_stack);
       wc.sel_smem = sel_bytes <= 40 * 1024 ? (int32_t)sel_bytes : 0;
     }
-    const int egrid = ctx->sm_count * ctx->blocks_per_sm;
-    if (fcap > 0) CK(cudaFuncSetAttribute(fsh.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast_smem));
+    P.egrid = ctx->sm_count * ctx->blocks_per_sm;
+    P.g_fast = ctx->sm_count * P.fsh->blocks;
+    if (P.use_fast) LCK(cudaFuncSetAttribute(P.fsh->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P.fast_smem));
     {
       /* longest-first processing order (ties: input order): counting sort over the lengths on
        * the host, which holds the offsets anyway */
       std::vector<int32_t> start(4098, 0);
       h_order.resize((size_t)m);
-      for (int k = 0; k < m; k++) {
-        const int si = round == 0 ? k : todo[k];
+      for (int q = 0; q < m; q++) {
+        const int si = round == 0 ? q : todo[q];
         start[4096 - (int)(h_offs[si + 1] - h_offs[si]) + 1]++;
       }
       for (int b = 0; b < 4097; b++) start[b + 1] += start[b];
-      for (int k = 0; k < m; k++) {
-        const int si = round == 0 ? k : todo[k];
+      for (int q = 0; q < m; q++) {
+        const int si = round == 0 ? q : todo[q];
         h_order[(size_t)start[4096 - (int)(h_offs[si + 1] - h_offs[si])]++] = si;
       }
-      CK(cudaMemcpyAsync(ctx->order.p, h_order.data(), sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, ctx->stream));
-      h2d_bytes += sizeof(int32_t) * (int64_t)m;
+      LCK(cudaMemcpyAsync(ln.order.p, h_order.data(), sizeof(int32_t) * (size_t)m, cudaMemcpyHostToDevice, ln.stream));
+      LCK(cudaStreamSynchronize(ln.stream)); /* h_order is pageable and reused */
+      T.h2d += sizeof(int32_t) * (int64_t)m;
     }
-    CK(cudaEventRecord(ctx->ev0, ctx->stream));
     for (int64_t w0 = 0; w0 < m; w0 += wave) {
       const int nw = (int)std::min<int64_t>(wave, m - w0);
-      wc.order = (const int32_t *)ctx->order.p + w0;
+      T.waves++;
+      wc.order = (const int32_t *)ln.order.p + w0;
       wc.n = nw;
+      P.nw = nw;
+      /* persistent block-scope kernels: a grid that fills the GPU once (occupancy x SMs), never
+       * more blocks than sequences */
+      auto grid_of = [&](const void *fn, int threads, size_t smem) {
+        int nb = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fn, threads, smem) != cudaSuccess || nb < 1) { (void)cudaGetLastError(); nb = 1; }
+        return (int)std::min<int64_t>(nw, (int64_t)nb * ctx->sm_count * ctx->persist);
+      };
+      P.g_gather = grid_of((const void *)k_gather, P.T_gather, 0);
+      P.g_combine = grid_of((const void *)k_combine, P.T_combine, P.stage_bytes);
+      P.g_select = grid_of((const void *)k_select, P.T_select, (size_t)wc.sel_smem);
+      P.g_mat = grid_of((const void *)k_materialise, P.T_mat, 0);
       /* every fold of an arena tags its `seen` entries with a new generation; when the 16-bit
        * counter wraps the tables are zeroed once */
-      if (++ctx->seen_gen > 65535u) {
-        CK(cudaMemsetAsync(ctx->arenas.p, 0, ctx->arena_clean, ctx->stream));
-        ctx->seen_gen = 1;
+      if (++ln.seen_gen > 65535u) {
+        LCK(cudaMemsetAsync(ln.arenas.p, 0, ln.arena_clean, ln.stream));
+        ln.seen_gen = 1;
       }
-      wc.prm.seen_gen = (int32_t)ctx->seen_gen;
-      k_init<<<nw, T, 0, ctx->stream>>>(wc);
-      launches++;
-      for (int it = 0;; it++) {
-        CK(cudaMemsetAsync(ctx->small.p, 0, 128, ctx->stream)); /* n_tasks, n_active, list counters, list cursors */
-        k_gather<<<nw, T_gather, 0, ctx->stream>>>(wc);
-        launches++;
-        if (fcap > 0) {
-          CK(cudaEventRecord(ctx->evx0, ctx->stream));
-          fsh.fn<<<ctx->sm_count * fsh.blocks, fsh.threads, fast_smem, ctx->stream>>>(wc);
-          CK(cudaEventRecord(ctx->evx1, ctx->stream));
-          launches++;
+      wc.prm.seen_gen = 0; /* the kernels read the generation from the control block */
+      h_prog[0] = 0; h_prog[1] = 0; /* the lane's stream is idle here: no kernel writes them now */
+      k_ctl_reset<<<1, 64, 0, ln.stream>>>(ctl, nw, (int)ln.seen_gen);
+      T.launches++;
+      const int per_iter = 1 + (P.use_fast ? 1 : 0) + (P.any_generic ? 5 : 0) + 3 + 1;
+      bool done = false;
+      if (!profile && ctx->loop_mode == 0) {
+        std::string why;
+        cudaGraphExec_t exec = wave_graph(ln, P, why);
+        if (exec) {
+          LCK(cudaGraphLaunch(exec, ln.stream));
+          done = true;
+        } else {
+          if (dbg) fprintf(stderr, "[rafft] launch graph unavailable (%s): stream loop\n", why.c_str());
+          ctx->loop_mode = 1;
         }
-        if (any_generic) {
-          k_expand<1><<<egrid, 128, 0, ctx->stream>>>(wc);
-          k_expand<2><<<egrid, 128, 0, ctx->stream>>>(wc);
-          k_expand<3><<<egrid, 128, 0, ctx->stream>>>(wc);
-          k_expand<4><<<egrid, 128, 0, ctx->stream>>>(wc);
-          k_expand<5><<<egrid, 128, 0, ctx->stream>>>(wc);
-          launches += 5;
-        }
-        k_combine<<<nw, T_combine, stage_bytes, ctx->stream>>>(wc);
-        k_select<<<nw, T_select, (size_t)wc.sel_smem, ctx->stream>>>(wc);
-        k_materialise<<<nw, T_mat, 0, ctx->stream>>>(wc);
-        launches += 3;
-        CK(cudaMemcpyAsync(ctx->h_small + 16, (int32_t *)ctx->small.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-        d2h += 8;
-        if (fcap > 0) {
-          float xms = 0.f;
-          CK(cudaEventElapsedTime(&xms, ctx->evx0, ctx->evx1));
-          expand_ms += xms;
-          expand_launches++;
-        }
-        const int32_t *hs = (const int32_t *)(ctx->h_small + 16);
-        if (hs[1] == 0) break;
-        if (it > 100000) { ctx->err = "rafft_fold_batch: no progress"; return fail(RAFFT_ERR_CUDA); }
       }
-      k_finish<<<nw, T_finish, 0, ctx->stream>>>(wc);
-      launches++;
+      if (!done) {
+        Emit E;
+        E.stream = ln.stream;
+        void *a_wc[] = {&wc};
+        cudaGraphConditionalHandle nohandle = 0;
+        if (profile) LCK(cudaEventRecord(ln.pev[0], ln.stream));
+        E.kernel((const void *)k_init, dim3(nw), dim3(P.T), 0, a_wc);
+        if (profile) {
+          /* stepwise: events around every kernel family, one host synchronisation per iteration */
+          LCK(cudaEventRecord(ln.pev[1], ln.stream));
+          LCK(cudaStreamSynchronize(ln.stream));
+          float ms = 0.f;
+          LCK(cudaEventElapsedTime(&ms, ln.pev[0], ln.pev[1]));
+          T.fam_ms[FAM_OTHER] += ms; T.fam_n[FAM_OTHER]++;
+          for (int it = 0; it < 1000000; it++) {
+            emit_iteration(E, P, nohandle, 0, ln.pev);
+            if (E.err != cudaSuccess) break;
+            LCK(cudaStreamSynchronize(ln.stream));
+            const int fams[7] = {FAM_GATHER, FAM_EXPAND_FAST, FAM_EXPAND_GENERIC, FAM_COMBINE, FAM_SELECT, FAM_MATERIALISE, FAM_ADVANCE};
+            for (int f = 0; f < 7; f++) {
+              LCK(cudaEventElapsedTime(&ms, ln.pev[f], ln.pev[f + 1]));
+              const bool ran = !(fams[f] == FAM_EXPAND_FAST && !P.use_fast) && !(fams[f] == FAM_EXPAND_GENERIC && !P.any_generic);
+              if (ran) { T.fam_ms[fams[f]] += ms; T.fam_n[fams[f]] += fams[f] == FAM_EXPAND_GENERIC ? 5 : 1; }
+            }
+            if (h_prog[1]) break;
+          }
+        } else {
+          /* stream loop: the host keeps at most 3 iterations ahead of the device (progress words in
+           * mapped host memory written by k_advance); iterations launched after the last live one
+           * find an empty active list and end at once */
+          volatile int32_t *hp = h_prog;
+          int launched = 0;
+          while (E.err == cudaSuccess && !hp[1]) {
+            if (launched - hp[0] < 3) { emit_iteration(E, P, nohandle, 0, nullptr); launched++; }
+            else std::this_thread::yield();
+          }
+        }
+        if (profile) LCK(cudaEventRecord(ln.pev[0], ln.stream));
+        E.kernel((const void *)k_finish, dim3(nw), dim3(P.T_finish), 0, a_wc);
+        if (profile) {
+          LCK(cudaEventRecord(ln.pev[1], ln.stream));
+          LCK(cudaStreamSynchronize(ln.stream));
+          float ms = 0.f;
+          LCK(cudaEventElapsedTime(&ms, ln.pev[0], ln.pev[1]));
+          T.fam_ms[FAM_OTHER] += ms; T.fam_n[FAM_OTHER]++;
+        }
+        if (E.err != cudaSuccess) { ln.err = std::string("kernel launch: ") + cudaGetErrorString(E.err); return RAFFT_ERR_CUDA; }
+      }
+      /* iterations of this wave (for the launch count) */
+      LCK(cudaMemcpyAsync(ln.h_small + 32, &ctl->iters, sizeof(int32_t), cudaMemcpyDeviceToHost, ln.stream));
+      LCK(cudaStreamSynchronize(ln.stream));
+      const int iters = *(const int32_t *)(ln.h_small + 32);
+      T.iters += iters;
+      T.launches += 2 + (int64_t)iters * per_iter;
+      T.d2h += 4;
       if (dbg) { /* high-water marks of the arena pieces against their capacities */
         std::vector<SeqState> hs((size_t)nw);
-        cudaMemcpyAsync(hs.data(), ctx->states.p, sizeof(SeqState) * (size_t)nw, cudaMemcpyDeviceToHost, ctx->stream);
-        cudaStreamSynchronize(ctx->stream);
+        cudaMemcpyAsync(hs.data(), ln.states.p, sizeof(SeqState) * (size_t)nw, cudaMemcpyDeviceToHost, ln.stream);
+        cudaStreamSynchronize(ln.stream);
         int hw[7] = {0, 0, 0, 0, 0, 0, 0};
         for (const SeqState &q : hs) {
           const int v[7] = {q.n_node, q.n_pool16, q.n_cand, q.n_store, q.n_nlist, q.n_seen, q.n_steps};
-          for (int k = 0; k < 7; k++) hw[k] = std::max(hw[k], v[k]);
+          for (int x = 0; x < 7; x++) hw[x] = std::max(hw[x], v[x]);
         }
-        fprintf(stderr, "[rafft] high water (cap): node %d (%d) pool16 %d (%d) cand %d (%d) store %d (%d) nlist %d (%d) seen %d (%d) steps %d (%d); arena %.1f MB, scale %d\n",
-                hw[0], caps.node_cap, hw[1], caps.pool16_cap, hw[2], caps.cand_cap, hw[3], caps.store_cap, hw[4], caps.nlist_cap,
+        fprintf(stderr, "[rafft] lane %d: %d iterations; high water (cap): node %d (%d) pool16 %d (%d) cand %d (%d) store %d (%d) nlist %d (%d) seen %d (%d) steps %d (%d); arena %.1f MB, scale %d\n",
+                k, iters, hw[0], caps.node_cap, hw[1], caps.pool16_cap, hw[2], caps.cand_cap, hw[3], caps.store_cap, hw[4], caps.nlist_cap,
                 hw[5], caps.seen_cap, hw[6], caps.step_cap, caps.arena_bytes / 1048576.0, scale);
       }
     }
-    CK(cudaEventRecord(ctx->ev1, ctx->stream));
-    CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(h_status.data(), O.status, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaMemcpyAsync(ctx->h_small, O.cursors, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
-    d2h += sizeof(int32_t) * (int64_t)n + 64;
-    float ms = 0.f;
-    CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
-    kernel_ms += ms;
-    for (int k = 0; k < 4; k++) used[k] = ctx->h_small[k];
+    LCK(cudaGetLastError());
+    LCK(cudaMemcpyAsync(T.h_status.data(), O.status, sizeof(int32_t) * (size_t)m_all, cudaMemcpyDeviceToHost, ln.stream));
+    LCK(cudaMemcpyAsync(ln.h_small, O.cursors, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ln.stream));
+    LCK(cudaStreamSynchronize(ln.stream));
+    ln.arena_dirty = false; /* every fold of the round ran to its end: the loop tables are clean */
+    T.d2h += sizeof(int32_t) * (int64_t)m_all + 64;
+    for (int q = 0; q < 4; q++) used[q] = ln.h_small[q];
     todo.clear();
-    for (int i = 0; i < n; i++)
-      if (h_status[i] == ST_ERR_CAPACITY) todo.push_back(i);
-    if (dbg && !todo.empty()) {
-      std::vector<int64_t> hc((size_t)n * CNT_N);
-      cudaMemcpy(hc.data(), O.counters, sizeof(int64_t) * hc.size(), cudaMemcpyDeviceToHost);
-      fprintf(stderr, "[rafft] round %d: %zu sequences over capacity (scale %d):", round, todo.size(), scale);
-      for (size_t k = 0; k < todo.size() && k < 12; k++)
-        fprintf(stderr, " #%d L=%lld line %lld;", todo[k], (long long)(h_offs[todo[k] + 1] - h_offs[todo[k]]), (long long)hc[(size_t)todo[k] * CNT_N + CNT_T1_NS]);
-      fprintf(stderr, "\n");
-    }
+    for (int i = 0; i < m_all; i++)
+      if (T.h_status[(size_t)i] == ST_ERR_CAPACITY) todo.push_back(i);
+    if (dbg && !todo.empty())
+      fprintf(stderr, "[rafft] lane %d round %d: %zu sequences over capacity (scale %d)\n", k, round, todo.size(), scale);
     if (todo.empty() || round >= 5) break;
     scale *= 4;
   }
 
-  lap("fold rounds done");
-  /* ordered layout on the device, then one copy per array into pinned host memory */
-  int64_t *d_scan = nullptr;
-  size_t scan_bytes = sizeof(int64_t) * (4 * (size_t)(n + 1) + 8);
-  if (int rc = dev_reserve(ctx, ctx->scan, scan_bytes)) return fail(rc);
-  d_scan = (int64_t *)ctx->scan.p;
+  /* ordered layout of this lane on the device */
+  const int n = m_all;
+  const size_t scan_bytes = sizeof(int64_t) * (7 * (size_t)(n + 1) + 8);
+  if (int rc = dev_reserve_s(ln.err, ln.scan, scan_bytes)) return rc;
+  int64_t *d_scan = (int64_t *)ln.scan.p;
   int64_t *d_struct_off = d_scan, *d_db_off = d_scan + (n + 1), *d_step_off = d_scan + 2 * (size_t)(n + 1),
-          *d_ent_base = d_scan + 3 * (size_t)(n + 1), *d_totals = d_scan + 4 * (size_t)(n + 1);
-  CK(cudaEventRecord(ctx->ev0, ctx->stream));
-  scan_kernel<<<1, 1024, 0, ctx->stream>>>(d_offs, n, O, d_struct_off, d_db_off, d_step_off, d_ent_base, d_totals);
-  launches++;
-  CK(cudaMemcpyAsync(ctx->h_small, d_totals, 4 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-  CK(cudaStreamSynchronize(ctx->stream));
-  d2h += 32;
-  const int64_t nS = ctx->h_small[0], nD = ctx->h_small[1], nT = ctx->h_small[2], nE = ctx->h_small[3];
-  /* device ordered buffer: energy | entry_struct | entry_off | db */
-  size_t o_energy = 0, o_entry = align_up(o_energy + sizeof(int32_t) * (size_t)nS, 256),
-         o_entoff = align_up(o_entry + sizeof(int32_t) * (size_t)nE, 256),
-         o_db = align_up(o_entoff + sizeof(int64_t) * (size_t)(nT + 1), 256),
-         o_end = align_up(o_db + (size_t)nD, 256);
-  if (int rc = dev_reserve(ctx, ctx->ordered, o_end)) return fail(rc);
-  char *dord = (char *)ctx->ordered.p;
+          *d_ent_base = d_scan + 3 * (size_t)(n + 1), *d_goff = d_scan + 4 * (size_t)(n + 1),
+          *d_totals = d_scan + 7 * (size_t)(n + 1);
   if (n > 0) {
-    pack_kernel<<<n, 256, 0, ctx->stream>>>(d_offs, n, O, d_struct_off, d_db_off, d_step_off, d_ent_base,
-                                           (int32_t *)(dord + o_energy), dord + o_db,
-                                           (int64_t *)(dord + o_entoff), (int32_t *)(dord + o_entry));
-    launches++;
-  } else {
-    CK(cudaMemsetAsync(dord + o_entoff, 0, sizeof(int64_t), ctx->stream));
+    scan_kernel<<<1, 1024, 0, ln.stream>>>(d_offs, n, O, d_struct_off, d_db_off, d_step_off, d_ent_base, d_totals);
+    T.launches++;
+    LCK(cudaMemcpyAsync(ln.h_small, d_totals, 4 * sizeof(int64_t), cudaMemcpyDeviceToHost, ln.stream));
+    LCK(cudaStreamSynchronize(ln.stream));
+    T.d2h += 32;
+    for (int q = 0; q < 4; q++) T.totals[q] = ln.h_small[q];
   }
-  CK(cudaEventRecord(ctx->ev1, ctx->stream));
-  CK(cudaGetLastError());
-  /* host block: [ordered part as on the device] status | struct_off | db_off | step_off | counters */
-  size_t h_status_o = o_end, h_soff = align_up(h_status_o + sizeof(int32_t) * (size_t)n, 16),
-         h_doff = h_soff + sizeof(int64_t) * (size_t)(n + 1), h_toff = h_doff + sizeof(int64_t) * (size_t)(n + 1),
-         h_cnt = h_toff + sizeof(int64_t) * (size_t)(n + 1), h_end = h_cnt + sizeof(int64_t) * (size_t)n * CNT_N;
-  lap("scan+pack queued");
-  if (int rc = host_block_get(ctx, h_end + 64, &R->block)) return fail(rc);
-  lap("host block");
-  char *hb = (char *)R->block.p;
-  CK(cudaMemcpyAsync(hb, dord, o_end, cudaMemcpyDeviceToHost, ctx->stream));
-  CK(cudaMemcpyAsync(hb + h_soff, d_scan, sizeof(int64_t) * 3 * (size_t)(n + 1), cudaMemcpyDeviceToHost, ctx->stream));
-  if (n > 0) CK(cudaMemcpyAsync(hb + h_cnt, O.counters, sizeof(int64_t) * (size_t)n * CNT_N, cudaMemcpyDeviceToHost, ctx->stream));
-  CK(cudaStreamSynchronize(ctx->stream));
-  d2h += (int64_t)o_end + (int64_t)sizeof(int64_t) * (3 * (n + 1) + (int64_t)n * CNT_N);
-  float ms2 = 0.f;
-  CK(cudaEventElapsedTime(&ms2, ctx->ev0, ctx->ev1));
-  kernel_ms += ms2;
-  lap("d2h done");
-  memcpy(hb + h_status_o, h_status.data(), sizeof(int32_t) * (size_t)n);
+  const int64_t nS = T.totals[0], nD = T.totals[1], nT = T.totals[2], nE = T.totals[3];
+  (void)nS; (void)nD; (void)nT; (void)nE;
+  T.O = O;
+  return RAFFT_OK;
+}
+
+/* second half of a lane: its results into the ordered layout (offsets continue after `base`, what
+ * the lanes before it hold) and into the job's host block */
+static int lane_pack(FoldJob &J, int k, const int64_t *base) {
+  LaneTask &T = J.lanes[(size_t)k];
+  rafft_ctx *ctx = T.ctx;
+  Lane &ln = ctx->lane[T.lane];
+  const int n = T.i1 - T.i0;
+  const int64_t *d_offs = T.d_offs + T.i0;
+  const OutBuf &O = T.O;
+  const int64_t nS = T.totals[0], nD = T.totals[1], nT = T.totals[2], nE = T.totals[3];
+  int64_t *d_scan = (int64_t *)ln.scan.p;
+  int64_t *d_struct_off = d_scan, *d_db_off = d_scan + (n + 1), *d_step_off = d_scan + 2 * (size_t)(n + 1),
+          *d_ent_base = d_scan + 3 * (size_t)(n + 1), *d_goff = d_scan + 4 * (size_t)(n + 1);
+  /* device ordered buffer: energy | entry_struct | entry_off | db */
+  const size_t o_energy = 0, o_entry = align_up(o_energy + sizeof(int32_t) * (size_t)nS, 256),
+               o_entoff = align_up(o_entry + sizeof(int32_t) * (size_t)nE, 256),
+               o_db = align_up(o_entoff + sizeof(int64_t) * (size_t)(nT + 1), 256),
+               o_end = align_up(o_db + (size_t)nD, 256);
+  if (int rc = dev_reserve_s(ln.err, ln.ordered, o_end)) return rc;
+  char *dord = (char *)ln.ordered.p;
+  if (n > 0) {
+    pack_kernel<<<n, 256, 0, ln.stream>>>(d_offs, n, O, d_struct_off, d_db_off, d_step_off, d_ent_base,
+                                         (int32_t *)(dord + o_energy), dord + o_db,
+                                         (int64_t *)(dord + o_entoff), (int32_t *)(dord + o_entry),
+                                         base[0], base[1], base[2], base[3], d_goff);
+    T.launches++;
+  }
+  LCK(cudaEventRecord(ln.ev1, ln.stream));
+  LCK(cudaGetLastError());
+  /* copy into the job's host block (skipped when a section would not fit: the job then gets a
+   * larger block and every lane copies again, lane_copy_out) */
+  bool fits;
+  {
+    std::lock_guard<std::mutex> lk(J.mu);
+    fits = true;
+    for (int q = 0; q < 4; q++) fits = fits && base[q] + T.totals[q] <= J.cap[q];
+  }
+  if (fits && n > 0) {
+    char *hb = (char *)J.block.p;
+    if (nS) LCK(cudaMemcpyAsync(hb + J.o_energy + sizeof(int32_t) * (size_t)base[0], dord + o_energy, sizeof(int32_t) * (size_t)nS, cudaMemcpyDeviceToHost, ln.stream));
+    if (nE) LCK(cudaMemcpyAsync(hb + J.o_entry + sizeof(int32_t) * (size_t)base[3], dord + o_entry, sizeof(int32_t) * (size_t)nE, cudaMemcpyDeviceToHost, ln.stream));
+    LCK(cudaMemcpyAsync(hb + J.o_entoff + sizeof(int64_t) * (size_t)base[2], dord + o_entoff, sizeof(int64_t) * (size_t)(nT + 1), cudaMemcpyDeviceToHost, ln.stream));
+    if (nD) LCK(cudaMemcpyAsync(hb + J.o_db + (size_t)base[1], dord + o_db, (size_t)nD, cudaMemcpyDeviceToHost, ln.stream));
+    LCK(cudaMemcpyAsync(hb + J.o_soff + sizeof(int64_t) * (size_t)T.i0, d_goff, sizeof(int64_t) * (size_t)(n + 1), cudaMemcpyDeviceToHost, ln.stream));
+    LCK(cudaMemcpyAsync(hb + J.o_doff + sizeof(int64_t) * (size_t)T.i0, d_goff + (n + 1), sizeof(int64_t) * (size_t)(n + 1), cudaMemcpyDeviceToHost, ln.stream));
+    LCK(cudaMemcpyAsync(hb + J.o_toff + sizeof(int64_t) * (size_t)T.i0, d_goff + 2 * (size_t)(n + 1), sizeof(int64_t) * (size_t)(n + 1), cudaMemcpyDeviceToHost, ln.stream));
+    LCK(cudaMemcpyAsync(hb + J.o_cnt + sizeof(int64_t) * (size_t)T.i0 * CNT_N, O.counters, sizeof(int64_t) * (size_t)n * CNT_N, cudaMemcpyDeviceToHost, ln.stream));
+    T.copied = true;
+    T.d2h += (int64_t)(sizeof(int32_t) * (size_t)(nS + nE) + sizeof(int64_t) * (size_t)(nT + 1) + (size_t)nD) +
+             (int64_t)sizeof(int64_t) * (3 * (n + 1) + (int64_t)n * CNT_N);
+  }
+  LCK(cudaStreamSynchronize(ln.stream));
+  LCK(cudaEventElapsedTime(&T.span_ms, ctx->ev_job, ln.ev1));
+  if (fits && n > 0) memcpy((char *)J.block.p + J.o_status + sizeof(int32_t) * (size_t)T.i0, T.h_status.data(), sizeof(int32_t) * (size_t)n);
+  return RAFFT_OK;
+}
+
+/* second chance after a host block that was too small: the lane's ordered buffer is still on the device */
+static int lane_copy_out(FoldJob &J, int k) {
+  LaneTask &T = J.lanes[(size_t)k];
+  rafft_ctx *ctx = T.ctx;
+  Lane &ln = ctx->lane[T.lane];
+  const int n = T.i1 - T.i0;
+  if (n <= 0) return RAFFT_OK;
+  LCK(cudaSetDevice(ctx->device));
+  const int64_t nS = T.totals[0], nD = T.totals[1], nT = T.totals[2], nE = T.totals[3];
+  const int64_t *base = J.cum[k];
+  const size_t o_energy = 0, o_entry = align_up(o_energy + sizeof(int32_t) * (size_t)nS, 256),
+               o_entoff = align_up(o_entry + sizeof(int32_t) * (size_t)nE, 256),
+               o_db = align_up(o_entoff + sizeof(int64_t) * (size_t)(nT + 1), 256);
+  char *dord = (char *)ln.ordered.p, *hb = (char *)J.block.p;
+  int64_t *d_goff = (int64_t *)ln.scan.p + 4 * (size_t)(n + 1);
+  OutBuf O;
+  memset(&O, 0, sizeof O);
+  idx_layout(O, (char *)ln.idx.p, n);
+  if (nS) LCK(cudaMemcpyAsync(hb + J.o_energy + sizeof(int32_t) * (size_t)base[0], dord + o_energy, sizeof(int32_t) * (size_t)nS, cudaMemcpyDeviceToHost, ln.stream));
+  if (nE) LCK(cudaMemcpyAsync(hb + J.o_entry + sizeof(int32_t) * (size_t)base[3], dord + o_entry, sizeof(int32_t) * (size_t)nE, cudaMemcpyDeviceToHost, ln.stream));
+  LCK(cudaMemcpyAsync(hb + J.o_entoff + sizeof(int64_t) * (size_t)base[2], dord + o_entoff, sizeof(int64_t) * (size_t)(nT + 1), cudaMemcpyDeviceToHost, ln.stream));
+  if (nD) LCK(cudaMemcpyAsync(hb + J.o_db + (size_t)base[1], dord + o_db, (size_t)nD, cudaMemcpyDeviceToHost, ln.stream));
+  LCK(cudaMemcpyAsync(hb + J.o_soff + sizeof(int64_t) * (size_t)T.i0, d_goff, sizeof(int64_t) * (size_t)(n + 1), cudaMemcpyDeviceToHost, ln.stream));
+  LCK(cudaMemcpyAsync(hb + J.o_doff + sizeof(int64_t) * (size_t)T.i0, d_goff + (n + 1), sizeof(int64_t) * (size_t)(n + 1), cudaMemcpyDeviceToHost, ln.stream));
+  LCK(cudaMemcpyAsync(hb + J.o_toff + sizeof(int64_t) * (size_t)T.i0, d_goff + 2 * (size_t)(n + 1), sizeof(int64_t) * (size_t)(n + 1), cudaMemcpyDeviceToHost, ln.stream));
+  LCK(cudaMemcpyAsync(hb + J.o_cnt + sizeof(int64_t) * (size_t)T.i0 * CNT_N, O.counters, sizeof(int64_t) * (size_t)n * CNT_N, cudaMemcpyDeviceToHost, ln.stream));
+  LCK(cudaStreamSynchronize(ln.stream));
+  memcpy(hb + J.o_status + sizeof(int32_t) * (size_t)T.i0, T.h_status.data(), sizeof(int32_t) * (size_t)n);
+  T.copied = true;
+  T.d2h += (int64_t)(sizeof(int32_t) * (size_t)(nS + nE) + sizeof(int64_t) * (size_t)(nT + 1) + (size_t)nD) +
+           (int64_t)sizeof(int64_t) * (3 * (n + 1) + (int64_t)n * CNT_N);
+  return RAFFT_OK;
+}
+
+static double seq_cost(int64_t L, int max_stack) { return (double)L * (double)L * (8.0 + max_stack) + 2000.0; }
+
+/* The fold proper.  ctxs[d] folds the sequences [dev_lo[d], dev_lo[d+1]) whose letters and offsets
+ * (all n + 1 of them) are at d_seqs[d] / d_offs[d] on its device; h_offs: host copy of the offsets. */
+static int fold_job(rafft_ctx *const *ctxs, int n_ctx, const int *dev_lo, const char *const *d_seqs,
+                    const int64_t *const *d_offs, const int64_t *h_offs, int32_t n, const rafft_params *params,
+                    rafft_result **out_res, int64_t h2d_bytes) {
+  rafft_ctx *ctx = ctxs[0]; /* owns the result and reports errors */
+  FoldJob J;
+  std::string err;
+  if (!build_fold_params(params, &J.F, err)) { ctx->err = "rafft_fold_batch: " + err; return RAFFT_ERR_ARG; }
+  for (int i = 0; i < n; i++) {
+    const int64_t L = h_offs[i + 1] - h_offs[i];
+    if (L < 0 || L > 4096) { ctx->err = "rafft_fold_batch: sequence length must be in [0, 4096]"; return RAFFT_ERR_ARG; }
+  }
+  J.n = n; J.h_offs = h_offs; J.params = params;
+  const FoldParams &F = J.F;
+  /* lanes: every device splits its range in two when the result copy is worth overlapping
+   * (the first half folds on the high-priority stream and is copied out while the second folds) */
+  for (int d = 0; d < n_ctx; d++) {
+    const int lo = dev_lo[d], hi = dev_lo[d + 1];
+    int64_t nt = h_offs[hi] - h_offs[lo];
+    int want = ctxs[d]->lanes;
+    if (want == 0) want = (nt * F.max_stack >= (int64_t)24 << 20 && hi - lo >= 512) ? 2 : 1;
+    if (ctxs[d]->profile || hi - lo < 2) want = 1;
+    int cut = hi;
+    if (want == 2) { /* equal estimated cost on both sides */
+      double tot = 0, run = 0;
+      for (int i = lo; i < hi; i++) tot += seq_cost(h_offs[i + 1] - h_offs[i], F.max_stack);
+      cut = lo;
+      while (cut < hi - 1 && run < 0.5 * tot) { run += seq_cost(h_offs[cut + 1] - h_offs[cut], F.max_stack); cut++; }
+      if (cut <= lo || cut >= hi) { want = 1; cut = hi; }
+    }
+    for (int l = 0; l < want; l++) {
+      LaneTask t;
+      t.ctx = ctxs[d]; t.lane = l;
+      t.i0 = l == 0 ? lo : cut; t.i1 = (l == 0 && want == 2) ? cut : hi;
+      t.d_seqs = d_seqs[d]; t.d_offs = d_offs[d];
+      t.first_of_ctx = l == 0;
+      J.lanes.push_back(t);
+    }
+  }
+  const int NL = (int)J.lanes.size();
+  memset(J.cum, 0, sizeof J.cum);
+  /* capacities of the host block's sections: exact bounds without trajectories, an estimate from the
+   * last call with them (a section that turns out too small costs a second copy, not the result) */
+  {
+    const int64_t total_nt = h_offs[n] - h_offs[0];
+    const double r = F.traj ? ctx->traj_ratio * 1.25 + 0.5 : 1.0;
+    J.cap[0] = (int64_t)((double)n * F.max_stack * r) + 16;
+    J.cap[1] = (int64_t)((double)total_nt * F.max_stack * r) + 256;
+    J.cap[2] = F.traj ? (int64_t)n * 40 + 16 : (int64_t)n + 1;
+    J.cap[3] = F.traj ? (int64_t)((double)n * F.max_stack * 16 * (r / 6.75)) + 64 : (int64_t)n * F.max_stack + 16;
+  }
+  job_layout(J);
+  ResultImpl *R = new ResultImpl;
+  memset(&R->pub, 0, sizeof R->pub);
+  R->ctx = ctx;
+  R->block = HostBlock();
+  auto cleanup = [&](int rc) {
+    /* one exit for every failure: the arenas of every lane that took part may hold a half-run fold */
+    for (LaneTask &t : J.lanes) t.ctx->lane[t.lane].arena_dirty = true;
+    R->block = J.block;
+    rafft_result_free(&R->pub);
+    return rc;
+  };
+  if (int rc = host_block_get(ctx, J.o_end, &J.block)) return cleanup(rc);
+  /* start-of-job event on every device: lanes time their span against it */
+  for (LaneTask &t : J.lanes) {
+    if (!t.first_of_ctx) continue;
+    if (cudaSetDevice(t.ctx->device) != cudaSuccess || cudaEventRecord(t.ctx->ev_job, t.ctx->lane[0].stream) != cudaSuccess) {
+      ctx->err = "rafft_fold_batch: cannot record the start event";
+      (void)cudaGetLastError();
+      return cleanup(RAFFT_ERR_CUDA);
+    }
+  }
+  auto run_lane = [&](int k) {
+    LaneTask &t = J.lanes[(size_t)k];
+    t.rc = lane_fold(J, k);
+    /* publish in lane order, whatever happened: the lanes behind wait for this */
+    int64_t base[4];
+    bool go;
+    {
+      std::unique_lock<std::mutex> lk(J.mu);
+      J.cv.wait(lk, [&] { return J.published >= k; });
+      if (t.rc != RAFFT_OK) J.abort = true;
+      for (int q = 0; q < 4; q++) {
+        base[q] = J.cum[k][q];
+        J.cum[k + 1][q] = base[q] + (t.rc == RAFFT_OK ? t.totals[q] : 0);
+        if (J.cum[k + 1][q] > J.cap[q]) J.overflow = true;
+      }
+      J.published = k + 1;
+      go = !J.abort;
+      J.cv.notify_all();
+    }
+    if (go) t.rc = lane_pack(J, k, base);
+  };
+  if (NL == 1) {
+    run_lane(0);
+  } else {
+    std::vector<std::thread> th;
+    for (int k = 1; k < NL; k++) th.emplace_back(run_lane, k);
+    run_lane(0);
+    for (auto &t : th) t.join();
+  }
+  cudaSetDevice(ctx->device);
+  for (int k = 0; k < NL; k++) {
+    LaneTask &t = J.lanes[(size_t)k];
+    if (t.rc != RAFFT_OK) {
+      ctx->err = "rafft_fold_batch: " + t.ctx->lane[t.lane].err;
+      return cleanup(t.rc);
+    }
+  }
+  if (J.abort) { ctx->err = "rafft_fold_batch: a lane failed"; return cleanup(RAFFT_ERR_CUDA); }
+  if (J.overflow) {
+    /* exact sizes are known now: a block that holds everything, every lane copies (again) */
+    HostBlock old = J.block;
+    for (int q = 0; q < 4; q++) J.cap[q] = J.cum[NL][q] + 16;
+    job_layout(J);
+    J.block = HostBlock();
+    { std::lock_guard<std::mutex> g(ctx->pin_mu); ctx->pinned_free.push_back(old); }
+    if (int rc = host_block_get(ctx, J.o_end, &J.block)) return cleanup(rc);
+    for (int k = 0; k < NL; k++) {
+      LaneTask &t = J.lanes[(size_t)k];
+      t.copied = false;
+      if (int rc = lane_copy_out(J, k)) { ctx->err = "rafft_fold_batch: " + t.ctx->lane[t.lane].err; return cleanup(rc); }
+    }
+    cudaSetDevice(ctx->device);
+  }
+  if (F.traj && n > 0) ctx->traj_ratio = std::max(1.0, (double)J.cum[NL][0] / ((double)n * F.max_stack));
+  char *hb = (char *)J.block.p;
+  if (n == 0) { /* no lane wrote anything: the four offset arrays hold their single 0 */
+    ((int64_t *)(hb + J.o_entoff))[0] = 0;
+    ((int64_t *)(hb + J.o_soff))[0] = 0; ((int64_t *)(hb + J.o_doff))[0] = 0; ((int64_t *)(hb + J.o_toff))[0] = 0;
+  }
+  R->block = J.block;
   rafft_result &P = R->pub;
   P.n_seq = n;
-  P.status = (const int32_t *)(hb + h_status_o);
-  P.struct_off = (const int64_t *)(hb + h_soff);
-  P.db_off = (const int64_t *)(hb + h_doff);
-  P.step_off = (const int64_t *)(hb + h_toff);
-  P.energy_dcal = (const int32_t *)(hb + o_energy);
-  P.db = hb + o_db;
-  P.entry_off = (const int64_t *)(hb + o_entoff);
-  P.entry_struct = (const int32_t *)(hb + o_entry);
-  P.counters = (const int64_t *)(hb + h_cnt);
-  P.kernel_ms = kernel_ms;
-  P.kernel_launches = launches;
+  P.status = (const int32_t *)(hb + J.o_status);
+  P.struct_off = (const int64_t *)(hb + J.o_soff);
+  P.db_off = (const int64_t *)(hb + J.o_doff);
+  P.step_off = (const int64_t *)(hb + J.o_toff);
+  P.energy_dcal = (const int32_t *)(hb + J.o_energy);
+  P.db = hb + J.o_db;
+  P.entry_off = (const int64_t *)(hb + J.o_entoff);
+  P.entry_struct = (const int32_t *)(hb + J.o_entry);
+  P.counters = (const int64_t *)(hb + J.o_cnt);
   P.h2d_bytes = h2d_bytes;
-  P.d2h_bytes = d2h;
-  P.expand_ms = expand_ms;
-  P.expand_launches = expand_launches;
+  for (LaneTask &t : J.lanes) {
+    P.kernel_ms = std::max(P.kernel_ms, (double)t.span_ms);
+    P.kernel_launches += t.launches;
+    P.h2d_bytes += t.h2d;
+    P.d2h_bytes += t.d2h;
+    P.iterations = std::max<int64_t>(P.iterations, t.iters);
+    for (int f = 0; f < FAM_N; f++) { P.family_ms[f] += t.fam_ms[f]; P.family_launches[f] += t.fam_n[f]; }
+  }
+  P.expand_ms = P.family_ms[FAM_EXPAND_FAST] + P.family_ms[FAM_EXPAND_GENERIC];
+  P.expand_launches = P.family_launches[FAM_EXPAND_FAST] + P.family_launches[FAM_EXPAND_GENERIC];
+  P.lanes = NL;
+  P.loop_mode = ctx->profile ? 2 : ctx->loop_mode;
   *out_res = &R->pub;
   return RAFFT_OK;
 }
@@ -942,23 +1579,65 @@ extern "C" {
 int rafft_fold_batch(rafft_ctx *ctx, const char *seqs, const int64_t *offs, int32_t n,
                      const rafft_params *params, rafft_result **out) {
   if (!ctx) return RAFFT_ERR_ARG;
+  return rafft_fold_batch_multi(&ctx, 1, seqs, offs, n, params, out);
+}
+
+int rafft_fold_batch_multi(rafft_ctx *const *ctxs, int32_t n_ctx, const char *seqs, const int64_t *offs, int32_t n,
+                           const rafft_params *params, rafft_result **out) {
+  if (!ctxs || n_ctx < 1 || n_ctx > RF_MAX_DEVICES || !ctxs[0]) return RAFFT_ERR_ARG;
+  rafft_ctx *ctx = ctxs[0];
+  for (int d = 0; d < n_ctx; d++) {
+    if (!ctxs[d]) { ctx->err = "rafft_fold_batch_multi: NULL context"; return RAFFT_ERR_ARG; }
+    for (int e = 0; e < d; e++)
+      if (ctxs[e] == ctxs[d] || ctxs[e]->device == ctxs[d]->device) { ctx->err = "rafft_fold_batch_multi: one context per device, each once"; return RAFFT_ERR_ARG; }
+  }
   if (!out || !params || n < 0 || (n > 0 && (!seqs || !offs))) { ctx->err = "rafft_fold_batch: bad argument"; return RAFFT_ERR_ARG; }
   *out = nullptr;
-  CK(cudaSetDevice(ctx->device));
   static const int64_t zero_offs[1] = {0};
   if (n == 0) offs = zero_offs;
   for (int i = 0; i < n; i++)
     if (offs[i + 1] < offs[i]) { ctx->err = "rafft_fold_batch: offsets must be non-decreasing"; return RAFFT_ERR_ARG; }
   const int64_t base = offs[0], total = offs[n] - base;
-  if (int rc = dev_reserve(ctx, ctx->seqs, (size_t)total + 16)) return rc;
-  if (int rc = dev_reserve(ctx, ctx->offs, sizeof(int64_t) * (size_t)(n + 1))) return rc;
-  std::vector<int64_t> rel(n + 1);
-  for (int i = 0; i <= n; i++) rel[i] = offs[i] - base;
-  if (total > 0) CK(cudaMemcpyAsync(ctx->seqs.p, seqs + base, (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
-  CK(cudaMemcpyAsync(ctx->offs.p, rel.data(), sizeof(int64_t) * (size_t)(n + 1), cudaMemcpyHostToDevice, ctx->stream));
-  CK(cudaStreamSynchronize(ctx->stream));
-  return fold_device(ctx, (const char *)ctx->seqs.p, (const int64_t *)ctx->offs.p, rel.data(), n, params, out,
-                     total + (int64_t)sizeof(int64_t) * (n + 1));
+  std::vector<int64_t> rel((size_t)n + 1);
+  for (int i = 0; i <= n; i++) rel[(size_t)i] = offs[i] - base;
+  /* contiguous ranges of the input order with equal estimated cost: every device's part of the
+   * result is then one contiguous piece of every output array */
+  if (n_ctx > n && n > 0) n_ctx = n;
+  if (n == 0) n_ctx = 1;
+  std::vector<int> dev_lo((size_t)n_ctx + 1, 0);
+  {
+    double tot = 0;
+    for (int i = 0; i < n; i++) tot += seq_cost(rel[(size_t)i + 1] - rel[(size_t)i], params->max_stack);
+    double run = 0;
+    int d = 1;
+    for (int i = 0; i < n && d < n_ctx; i++) {
+      run += seq_cost(rel[(size_t)i + 1] - rel[(size_t)i], params->max_stack);
+      while (d < n_ctx && run >= tot * d / n_ctx && i + 1 <= n - (n_ctx - d)) dev_lo[(size_t)d++] = i + 1;
+    }
+    for (; d < n_ctx; d++) dev_lo[(size_t)d] = std::max(dev_lo[(size_t)d - 1] + 1, n - (n_ctx - d));
+    dev_lo[(size_t)n_ctx] = n;
+  }
+  std::vector<const char *> d_seqs((size_t)n_ctx);
+  std::vector<const int64_t *> d_offs((size_t)n_ctx);
+  int64_t h2d = 0;
+  for (int d = 0; d < n_ctx; d++) {
+    rafft_ctx *cx = ctxs[d];
+    cudaError_t e = cudaSetDevice(cx->device);
+    if (e != cudaSuccess) { ctx->err = std::string("cudaSetDevice: ") + cudaGetErrorString(e); return RAFFT_ERR_CUDA; }
+    if (int rc = dev_reserve(cx, cx->seqs, (size_t)total + 16)) { ctx->err = cx->err; return rc; }
+    if (int rc = dev_reserve(cx, cx->offs, sizeof(int64_t) * (size_t)(n + 1))) { ctx->err = cx->err; return rc; }
+    /* every device gets the letters of its own range and all offsets */
+    const int64_t lo = rel[(size_t)dev_lo[(size_t)d]], hi = rel[(size_t)dev_lo[(size_t)d + 1]];
+    if (hi > lo) e = cudaMemcpyAsync((char *)cx->seqs.p + lo, seqs + base + lo, (size_t)(hi - lo), cudaMemcpyHostToDevice, cx->lane[0].stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(cx->offs.p, rel.data(), sizeof(int64_t) * (size_t)(n + 1), cudaMemcpyHostToDevice, cx->lane[0].stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(cx->lane[0].stream);
+    if (e != cudaSuccess) { ctx->err = std::string("input copy: ") + cudaGetErrorString(e); return RAFFT_ERR_CUDA; }
+    h2d += (hi - lo) + (int64_t)sizeof(int64_t) * (n + 1);
+    d_seqs[(size_t)d] = (const char *)cx->seqs.p;
+    d_offs[(size_t)d] = (const int64_t *)cx->offs.p;
+  }
+  cudaSetDevice(ctx->device);
+  return fold_job(ctxs, n_ctx, dev_lo.data(), d_seqs.data(), d_offs.data(), rel.data(), n, params, out, h2d);
 }
 
 int rafft_fold_batch_device(rafft_ctx *ctx, const void *d_seqs, const void *d_offs, int32_t n,
@@ -970,12 +1649,39 @@ int rafft_fold_batch_device(rafft_ctx *ctx, const void *d_seqs, const void *d_of
   *out = nullptr;
   CK(cudaSetDevice(ctx->device));
   /* the offsets (8(n+1) bytes) are needed on the host to size the arenas and the result */
-  std::vector<int64_t> h_offs(n + 1, 0);
+  std::vector<int64_t> h_offs((size_t)n + 1, 0);
   if (n > 0) CK(cudaMemcpy(h_offs.data(), d_offs, sizeof(int64_t) * (size_t)(n + 1), cudaMemcpyDeviceToHost));
   if (n > 0 && h_offs[0] != 0) { ctx->err = "rafft_fold_batch_device: offs[0] must be 0"; return RAFFT_ERR_ARG; }
   for (int i = 0; i < n; i++)
-    if (h_offs[i + 1] < h_offs[i]) { ctx->err = "rafft_fold_batch_device: offsets must be non-decreasing"; return RAFFT_ERR_ARG; }
-  return fold_device(ctx, (const char *)d_seqs, (const int64_t *)d_offs, h_offs.data(), n, params, out, 0);
+    if (h_offs[(size_t)i + 1] < h_offs[(size_t)i]) { ctx->err = "rafft_fold_batch_device: offsets must be non-decreasing"; return RAFFT_ERR_ARG; }
+  const int dev_lo[2] = {0, n};
+  const char *ds = (const char *)d_seqs;
+  const int64_t *dofs = (const int64_t *)d_offs;
+  return fold_job(&ctx, 1, dev_lo, &ds, &dofs, h_offs.data(), n, params, out, 0);
+}
+
+int rafft_int_peak(rafft_ctx *ctx, double *issue_warp_inst_per_s, double *mix_warp_inst_per_s) {
+  if (!ctx || !issue_warp_inst_per_s) return RAFFT_ERR_ARG;
+  CK(cudaSetDevice(ctx->device));
+  if (int rc = dev_reserve(ctx, ctx->peakbuf, 256)) return rc;
+  const int iters = 1500, blocks = ctx->sm_count * 8;
+  Lane &ln = ctx->lane[0];
+  double best[2] = {0, 0};
+  for (int mode = 0; mode < 2; mode++) {
+    for (int rep = 0; rep < 4; rep++) {
+      CK(cudaEventRecord(ln.pev[0], ln.stream));
+      int_peak_kernel<<<blocks, 256, 0, ln.stream>>>((unsigned *)ctx->peakbuf.p, iters, 7u + rep, mode);
+      CK(cudaEventRecord(ln.pev[1], ln.stream));
+      CK(cudaStreamSynchronize(ln.stream));
+      float ms = 0.f;
+      CK(cudaEventElapsedTime(&ms, ln.pev[0], ln.pev[1]));
+      const double winst = (double)blocks * 8.0 * iters * 16.0 * 8.0;
+      if (rep > 0) best[mode] = std::max(best[mode], winst / (ms * 1e-3));
+    }
+  }
+  *issue_warp_inst_per_s = best[0];                        /* IADD3 stream: every scheduler issues every cycle */
+  if (mix_warp_inst_per_s) *mix_warp_inst_per_s = best[1];  /* IADD3/LOP3 alternating (LOP3 runs at half rate) */
+  return RAFFT_OK;
 }
 
 int rafft_eval_structures(rafft_ctx *ctx, const char *seqs, const char *structs, const int64_t *offs,

@@ -41,6 +41,21 @@ class FoldContext:
     def _err(self, rc):
         return N.NativeError(rc, (self._lib.rafft_last_error(self._h) or b"").decode())
 
+    def set_option(self, name, value):
+        "tuning / diagnostics switch of the context (include/rafft_b200.h rafft_set_option)"
+        rc = self._lib.rafft_set_option(self._h, name.encode(), int(value))
+        if rc != N.RAFFT_OK:
+            raise self._err(rc)
+
+    def int_peak(self):
+        """(issue-slot peak, IADD3/LOP3 mix) in warp-instructions per second, measured now on this
+        context's device by the library's microbenchmark kernel"""
+        a, b = C.c_double(), C.c_double()
+        rc = self._lib.rafft_int_peak(self._h, C.byref(a), C.byref(b))
+        if rc != N.RAFFT_OK:
+            raise self._err(rc)
+        return a.value, b.value
+
     # -- raw calls ---------------------------------------------------------------------
     def fold_raw(self, seq_bytes, offs, params):
         """seq_bytes: concatenated ASCII letters; offs: int64 numpy array (n+1).
@@ -82,6 +97,22 @@ class FoldContext:
         return out[:n]
 
 
+def fold_raw_multi(contexts, seq_bytes, offs, params):
+    """One batch folded by several devices from this process (rafft_fold_batch_multi): contiguous
+    ranges of the input order, one host thread + stream per device inside the library, one result
+    in input order.  contexts: FoldContext objects of different devices; the first owns the result."""
+    offs = np.ascontiguousarray(offs, dtype=np.int64)
+    n = len(offs) - 1
+    res = C.POINTER(N.Result)()
+    lib = contexts[0]._lib
+    hs = (C.c_void_p * len(contexts))(*[c._h.value for c in contexts])
+    rc = lib.rafft_fold_batch_multi(hs, len(contexts), seq_bytes, offs.ctypes.data_as(C.POINTER(C.c_int64)),
+                                    n, C.byref(params), C.byref(res))
+    if rc != N.RAFFT_OK:
+        raise contexts[0]._err(rc)
+    return RawResult(res, offs, lib, contexts[0])
+
+
 def _np(ptr, count, dtype):
     if count == 0:
         return np.zeros(0, dtype=dtype)
@@ -102,6 +133,10 @@ class RawResult:
         self.kernel_launches = r.kernel_launches
         self.expand_ms = r.expand_ms
         self.expand_launches = r.expand_launches
+        self.iterations = r.iterations
+        self.family_ms = dict(zip(N.FAMILY_NAMES, r.family_ms))
+        self.family_launches = dict(zip(N.FAMILY_NAMES, r.family_launches))
+        self.lanes, self.loop_mode = r.lanes, r.loop_mode
         self.h2d_bytes, self.d2h_bytes = r.h2d_bytes, r.d2h_bytes
         self.status = _np(r.status, n, np.int32)
         self.struct_off = _np(r.struct_off, n + 1, np.int64)

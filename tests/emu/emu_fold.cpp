@@ -72,6 +72,7 @@ int emu_fold(const rafft_energy_params *ep_in, const char *seq, int L, const raf
    * first one left behind under another generation tag */
   for (int gen = 1; gen <= 2; gen++) {
   F.seen_gen = gen;
+  f.gen = gen;
   n_tasks = 0;
   cursors[0] = cursors[1] = cursors[2] = cursors[3] = cursors[4] = cursors[5] = cursors[6] = cursors[7] = 0;
   f.phase_init(seq, L, 0);
