@@ -146,6 +146,10 @@ void rafft_result_free(rafft_result *res);
 int rafft_fold_batch_multi(rafft_ctx *const *ctxs, int32_t n_ctx, const char *seqs, const int64_t *offs,
                            int32_t n, const rafft_params *params, rafft_result **out);
 
+/* The ranges rafft_fold_batch_multi deals to `parts` devices: lo[p] .. lo[p+1] (parts + 1 values),
+ * contiguous in input order, equal estimated cost (~ L^2 (8 + max_stack)).  Needs no device. */
+int rafft_plan_ranges(const int64_t *offs, int32_t n, int32_t parts, int32_t max_stack, int32_t *lo);
+
 /* Same, but the inputs already live in device memory (d_seqs: the concatenated letters,
  * d_offs: n+1 int64) and the timed work is the kernel only; results are still returned on
  * the host.  Used by bench.py for the device-resident figure. */

@@ -1235,7 +1235,13 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
               LCK(cudaEventElapsedTime(&ms, ln.pev[f], ln.pev[f + 1]));
               const bool ran = !(fams[f] == FAM_EXPAND_FAST && !P.use_fast) && !(fams[f] == FAM_EXPAND_GENERIC && !P.any_generic);
               if (ran) { T.fam_ms[fams[f]] += ms; T.fam_n[fams[f]] += fams[f] == FAM_EXPAND_GENERIC ? 5 : 1; }
+              if (dbg) {
+                static const char *const nm[7] = {"gather", "fast", "generic", "combine", "select", "materialise", "advance"};
+                if (f == 0) fprintf(stderr, "[rafft] it %2d:", it);
+                fprintf(stderr, "  %s %.3f", nm[f], ms);
+              }
             }
+            if (dbg) fprintf(stderr, "  ms\n");
             if (h_prog[1]) break;
           }
         } else {
@@ -1411,6 +1417,24 @@ static int lane_copy_out(FoldJob &J, int k) {
 }
 
 static double seq_cost(int64_t L, int max_stack) { return (double)L * (double)L * (8.0 + max_stack) + 2000.0; }
+
+/* n sequences (offsets offs[0..n]) dealt to `parts` consumers as contiguous ranges of the input
+ * order with equal estimated cost; every range is non-empty when n >= parts.  lo: parts + 1. */
+static void plan_ranges(const int64_t *offs, int n, int parts, int max_stack, int *lo) {
+  double tot = 0;
+  for (int i = 0; i < n; i++) tot += seq_cost(offs[i + 1] - offs[i], max_stack);
+  lo[0] = 0;
+  double run = 0;
+  int d = 1;
+  for (int i = 0; i < n && d < parts; i++) {
+    run += seq_cost(offs[i + 1] - offs[i], max_stack);
+    /* close part d-1 after sequence i once it holds its share -- or when the sequences left are
+     * just enough to give every later part one */
+    while (d < parts && i + 1 > lo[d - 1] && (run >= tot * d / parts || n - (i + 1) <= parts - d)) lo[d++] = i + 1;
+  }
+  for (; d < parts; d++) lo[d] = n;
+  lo[parts] = n;
+}
 
 /* The fold proper.  ctxs[d] folds the sequences [dev_lo[d], dev_lo[d+1]) whose letters and offsets
  * (all n + 1 of them) are at d_seqs[d] / d_offs[d] on its device; h_offs: host copy of the offsets. */
@@ -1605,18 +1629,7 @@ int rafft_fold_batch_multi(rafft_ctx *const *ctxs, int32_t n_ctx, const char *se
   if (n_ctx > n && n > 0) n_ctx = n;
   if (n == 0) n_ctx = 1;
   std::vector<int> dev_lo((size_t)n_ctx + 1, 0);
-  {
-    double tot = 0;
-    for (int i = 0; i < n; i++) tot += seq_cost(rel[(size_t)i + 1] - rel[(size_t)i], params->max_stack);
-    double run = 0;
-    int d = 1;
-    for (int i = 0; i < n && d < n_ctx; i++) {
-      run += seq_cost(rel[(size_t)i + 1] - rel[(size_t)i], params->max_stack);
-      while (d < n_ctx && run >= tot * d / n_ctx && i + 1 <= n - (n_ctx - d)) dev_lo[(size_t)d++] = i + 1;
-    }
-    for (; d < n_ctx; d++) dev_lo[(size_t)d] = std::max(dev_lo[(size_t)d - 1] + 1, n - (n_ctx - d));
-    dev_lo[(size_t)n_ctx] = n;
-  }
+  plan_ranges(rel.data(), n, n_ctx, params->max_stack, dev_lo.data());
   std::vector<const char *> d_seqs((size_t)n_ctx);
   std::vector<const int64_t *> d_offs((size_t)n_ctx);
   int64_t h2d = 0;
@@ -1658,6 +1671,14 @@ int rafft_fold_batch_device(rafft_ctx *ctx, const void *d_seqs, const void *d_of
   const char *ds = (const char *)d_seqs;
   const int64_t *dofs = (const int64_t *)d_offs;
   return fold_job(&ctx, 1, dev_lo, &ds, &dofs, h_offs.data(), n, params, out, 0);
+}
+
+int rafft_plan_ranges(const int64_t *offs, int32_t n, int32_t parts, int32_t max_stack, int32_t *lo) {
+  if (!offs || !lo || n < 0 || parts < 1) return RAFFT_ERR_ARG;
+  for (int i = 0; i < n; i++)
+    if (offs[i + 1] < offs[i]) return RAFFT_ERR_ARG;
+  plan_ranges(offs, n, parts, max_stack, lo);
+  return RAFFT_OK;
 }
 
 int rafft_int_peak(rafft_ctx *ctx, double *issue_warp_inst_per_s, double *mix_warp_inst_per_s) {

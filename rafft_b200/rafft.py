@@ -11,7 +11,6 @@ import numpy as np
 from . import _native as N
 from .utils import Structure, energy_from_dcal
 
-_VALID = frozenset("ACGU")
 
 
 class FoldContext:
@@ -200,48 +199,115 @@ def get_context(device=0):
     return ctx
 
 
+def _structure(db, e):
+    st = Structure()
+    st.str_struct = db
+    st.energy_dcal = e
+    st.energy = energy_from_dcal(e)
+    return st
+
+
 def _structures(step):
-    out = []
-    for db, e in step:
-        st = Structure()
-        st.str_struct = db
-        st.energy_dcal = e
-        st.energy = energy_from_dcal(e)
-        out.append(st)
-    return out
+    return [_structure(db, e) for db, e in step]
 
 
-def _check_letters(sequence):
-    for ch in sequence:
-        if ch not in _VALID:
-            # the reference fails with KeyError in prep_sequence (rafft/utils.py:73-80); its
-            # `N` rows are all-zero and ViennaRNA treats N specially: not supported here
-            raise KeyError(ch)
+_LETTER_OK = np.zeros(256, dtype=bool)
+_LETTER_OK[[ord(c) for c in "ACGU"]] = True
+
+
+def _check_letters(seq_bytes):
+    """One vectorised pass over the joined letters.  The reference fails with KeyError in
+    prep_sequence (rafft/utils.py:73-80) for letters outside its table; its `N` rows are all-zero
+    and ViennaRNA treats N specially: not supported here."""
+    arr = np.frombuffer(seq_bytes, dtype=np.uint8)
+    bad = ~_LETTER_OK[arr]
+    if bad.any():
+        raise KeyError(chr(int(arr[int(np.argmax(bad))])))
+
+
+class BatchFolds:
+    """What fold_batch returns: a read-only sequence with one `fold`-style result per input
+    sequence -- a list of Structure, or (list, trajectory) with traj=True -- built on access from
+    zero-copy views of the library's result arrays (nothing is converted for sequences nobody
+    looks at).  `.raw` is the RawResult (numpy views: energy, db, offsets) for bulk consumers."""
+
+    def __init__(self, raw, traj):
+        self.raw, self._traj = raw, traj
+        bad = np.nonzero(raw.status != N.RAFFT_OK)[0]
+        if len(bad):
+            i = int(bad[0])
+            raise N.NativeError(int(raw.status[i]), "sequence %d could not be folded" % i)
+
+    def __len__(self):
+        return self.raw.n_seq
+
+    def _beam(self, i, t):
+        raw = self.raw
+        L = int(raw.lengths[i])
+        s0, d0 = int(raw.struct_off[i]), int(raw.db_off[i])
+        ks = raw.entry_struct[int(raw.entry_off[t]):int(raw.entry_off[t + 1])]
+        if L == 0 or len(ks) == 0:
+            return []
+        n_s = int(raw.struct_off[i + 1]) - s0
+        rows = raw.db[d0:d0 + n_s * L].reshape(n_s, L)[ks]       # one gather for the whole beam
+        text = rows.tobytes().decode("ascii")
+        es = raw.energy[s0 + ks].tolist()
+        return [_structure(text[k * L:(k + 1) * L], e) for k, e in enumerate(es)]
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[k] for k in range(*i.indices(len(self)))]
+        if i < 0:
+            i += len(self)
+        if not 0 <= i < len(self):
+            raise IndexError(i)
+        t0, t1 = int(self.raw.step_off[i]), int(self.raw.step_off[i + 1])
+        final = self._beam(i, t1 - 1)
+        if not self._traj:
+            return final
+        return final, [self._beam(i, t) for t in range(t0, t1 - 1)] + [final]
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
+
+    def best(self):
+        """(dot-bracket bytes as uint8 rows are ragged, so:) lists of the lowest-energy structure of
+        every sequence and its energy in dcal/mol -- the `rafft --bench` first line, vectorised."""
+        raw = self.raw
+        last = raw.step_off[1:] - 1
+        first_entry = raw.entry_struct[raw.entry_off[last]] + raw.struct_off[:-1]
+        e = raw.energy[first_entry]
+        L = raw.lengths
+        start = raw.db_off[:-1] + (first_entry - raw.struct_off[:-1]) * L
+        buf = raw.db
+        return [buf[int(a):int(a + l)].tobytes().decode("ascii") for a, l in zip(start, L)], e
 
 
 def fold_batch(sequences, nb_mode=100, max_stack=1, max_branch=100, min_hp=3, min_nrj=0.0,
-               traj=False, temp=37.0, gc_wei=3.0, au_wei=2.0, gu_wei=1.0, device=0, context=None):
-    """Fold many sequences in one library call.  Returns one `fold`-style result per
-    sequence (list of Structure, or (list, trajectory) with traj=True)."""
+               traj=False, temp=37.0, gc_wei=3.0, au_wei=2.0, gu_wei=1.0, device=0, context=None,
+               devices=None):
+    """Fold many sequences in one library call.  Returns a BatchFolds: one `fold`-style result per
+    sequence (list of Structure, or (list, trajectory) with traj=True), materialised on access.
+    devices=[d0, d1, ...] folds the batch on several GPUs from this one process (contiguous
+    ranges of the input, one host thread + stream per device inside the library, results in input
+    order) -- the replacement of the reference's process pool over the sequences of a set
+    (benchmark_results/bench_fft.py:17-22)."""
     sequences = list(sequences)
-    for s in sequences:
-        _check_letters(s)
-        if len(s) == 0:
-            raise ValueError("empty sequence")
-    ctx = context if context is not None else get_context(device)
+    lens = np.fromiter(map(len, sequences), dtype=np.int64, count=len(sequences))
+    if len(lens) and int(lens.min()) == 0:
+        raise ValueError("empty sequence")
+    seq_bytes = "".join(sequences).encode("ascii", "replace")
+    _check_letters(seq_bytes)
     offs = np.zeros(len(sequences) + 1, dtype=np.int64)
-    np.cumsum([len(s) for s in sequences], out=offs[1:])
+    np.cumsum(lens, out=offs[1:])
     params = make_params(nb_mode, max_stack, max_branch, min_hp, min_nrj, traj, temp, gc_wei,
                          au_wei, gu_wei)
-    raw = ctx.fold_raw("".join(sequences).encode(), offs, params)
-    out = []
-    for i in range(len(sequences)):
-        if raw.status[i] != N.RAFFT_OK:
-            raise N.NativeError(int(raw.status[i]), "sequence %d could not be folded" % i)
-        steps = raw.steps(i)
-        final = _structures(steps[-1])
-        out.append((final, [_structures(s) for s in steps]) if traj else final)
-    return out
+    if devices is not None and len(devices) > 1:
+        raw = fold_raw_multi([get_context(d) for d in devices], seq_bytes, offs, params)
+    else:
+        ctx = context if context is not None else get_context(devices[0] if devices else device)
+        raw = ctx.fold_raw(seq_bytes, offs, params)
+    return BatchFolds(raw, traj)
 
 
 def fold(sequence, nb_mode=100, max_stack=1, max_branch=100, min_hp=3, min_nrj=0.0, traj=False,

@@ -27,6 +27,22 @@ def partition(lengths, world_size, max_stack=50):
     return [np.array(sorted(s), dtype=np.int64) for s in shards]
 
 
+def plan_ranges(lengths, parts, max_stack=50):
+    """The contiguous ranges of the input order that the single-process multi-device entry
+    (rafft_fold_batch_multi, `fold_batch(..., devices=[...])`) deals to `parts` devices: parts + 1
+    boundaries, equal estimated cost.  Computed by the library (no device needed)."""
+    import ctypes as C
+    from . import _native as N
+    offs = np.zeros(len(lengths) + 1, dtype=np.int64)
+    np.cumsum(np.asarray(lengths, dtype=np.int64), out=offs[1:])
+    lo = np.zeros(parts + 1, dtype=np.int32)
+    rc = N.lib().rafft_plan_ranges(offs.ctypes.data_as(C.POINTER(C.c_int64)), len(lengths), parts, max_stack,
+                                   lo.ctypes.data_as(C.POINTER(C.c_int32)))
+    if rc != N.RAFFT_OK:
+        raise ValueError("rafft_plan_ranges failed: %d" % rc)
+    return lo
+
+
 def imbalance(lengths, shards, max_stack=50):
     "max shard cost / mean shard cost under the cost model"
     c = [sum(estimated_cost(lengths[i], max_stack) for i in s) for s in shards]

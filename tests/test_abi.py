@@ -62,9 +62,9 @@ def test_no_cpu_fallback_without_gpu(native_lib_path):
 
 def test_product_does_not_reference_oracle():
     "nothing in the shipped package imports, links or names oracle/"
-    pkg = os.path.join(ROOT, "rafft_b200")
-    for dp, _, fs in os.walk(pkg):
-        for f in fs:
-            if f.endswith((".py", ".cu", ".cuh", ".h")):
-                txt = open(os.path.join(dp, f)).read()
-                assert "pyoracle" not in txt and "liboracle" not in txt and "oracle_" not in txt, f
+    for pkg in ("rafft_b200", "rafft", "bin", "include"):
+        for dp, _, fs in os.walk(os.path.join(ROOT, pkg)):
+            for f in fs:
+                if f.endswith((".py", ".cu", ".cuh", ".h")) or pkg == "bin":
+                    txt = open(os.path.join(dp, f), errors="replace").read()
+                    assert "pyoracle" not in txt and "liboracle" not in txt and "oracle_" not in txt, f

@@ -94,23 +94,87 @@ def test_kernel_kats_through_the_path(ctx, kernel_kat, oracle):
 
 
 # ---- batches vs oracle -----------------------------------------------------------------
-def test_batch_cfg2_sample_vs_oracle(ctx, oracle):
-    "every 20th sequence of the 10k benchmark batch at -n 100 -ms 50 (BASELINE config 2)"
-    seqs = config_batch("cfg2")[::20]
-    got, raw = gpu_steps(ctx, seqs, nb_mode=100, max_stack=50)
-    want, cnt = oracle.fold_batch(seqs, 100, 50, 1000)
-    bad = [i for i in range(len(seqs)) if got[i] != want[i]]
-    assert not bad, bad[:5]
-    # reference-formulation work counters agree too
-    assert (raw.counters[:, :5] == cnt[:, :5]).all() and (raw.counters[:, 8:10] == cnt[:, 8:10]).all()
+def fold_and_check(ctx, oracle, seqs, nb_mode, max_stack, traj=True, counters=True):
+    """the whole batch through the C-ABI, then every beam of every sequence (energies, dot-brackets,
+    order; with traj every folding step) against the oracle's own fold, compared inside the oracle
+    library; the reference-formulation work counters too"""
+    from rafft_b200 import rafft as R
+    offs = np.zeros(len(seqs) + 1, dtype=np.int64)
+    np.cumsum([len(s) for s in seqs], out=offs[1:])
+    raw = ctx.fold_raw("".join(seqs).encode(), offs, R.make_params(nb_mode, max_stack, 1000, traj=traj))
+    assert (raw.status == 0).all(), np.bincount(raw.status)
+    bad, cnt = oracle.fold_batch_check(seqs, raw, nb_mode, max_stack, 1000, traj=traj)
+    assert not bad, "%d sequences differ from the oracle, first %s" % (len(bad), bad[:5])
+    if counters:
+        assert (raw.counters[:, :5] == cnt[:, :5]).all() and (raw.counters[:, 8:10] == cnt[:, 8:10]).all()
+    return raw
 
 
-def test_batch_cfg3_sample_vs_oracle(ctx, oracle):
-    "-n 200 -ms 200 (BASELINE config 3) on a sample"
-    seqs = config_batch("cfg2")[7::250]
-    got, _ = gpu_steps(ctx, seqs, nb_mode=200, max_stack=200)
-    want, _ = oracle.fold_batch(seqs, 200, 200, 1000)
-    assert got == want
+def test_full_batch_cfg2_vs_oracle(ctx, oracle):
+    "BASELINE configs[1]: ALL 10,000 sequences at -n 100 -ms 50, whole trajectories, bit-exact"
+    raw = fold_and_check(ctx, oracle, config_batch("cfg2"), 100, 50)
+    assert raw.n_seq == 10000
+
+
+def test_batch_cfg3_2500_vs_oracle(ctx, oracle):
+    "BASELINE configs[2]: every 4th sequence of the 10k batch at -n 200 -ms 200, whole trajectories"
+    fold_and_check(ctx, oracle, config_batch("cfg2")[1::4], 200, 200)
+
+
+def test_cfg3_full_batch_final_beams_vs_oracle(ctx, oracle):
+    "BASELINE configs[2] as benchmarked (no trajectory): the final 200 structures of a 1,250-sequence GPU share"
+    fold_and_check(ctx, oracle, config_batch("cfg2")[3::8], 200, 200, traj=False)
+
+
+def test_lanes_and_loop_modes_give_identical_results(ctx):
+    """one lane / two lanes (two priority streams, result copy of the first overlapping the fold of the
+    second), graph WHILE loop / stream loop with look-ahead / stepwise profile mode: same bytes"""
+    from rafft_b200 import rafft as R
+    seqs = config_batch("cfg2", 1500)
+    offs = np.zeros(len(seqs) + 1, dtype=np.int64)
+    np.cumsum([len(s) for s in seqs], out=offs[1:])
+    sb, prm = "".join(seqs).encode(), R.make_params(100, 50, 1000, traj=True)
+    ref = None
+    try:
+        for lanes, loop, prof in ((1, 0, 0), (2, 0, 0), (2, 1, 0), (1, 1, 0), (1, 0, 1), (2, 0, 0)):
+            ctx.set_option("lanes", lanes); ctx.set_option("loop", loop); ctx.set_option("profile", prof)
+            raw = ctx.fold_raw(sb, offs, prm)
+            assert raw.lanes == lanes and raw.loop_mode == (2 if prof else loop)
+            cur = [np.array(a) for a in (raw.status, raw.struct_off, raw.energy, raw.db_off, raw.db, raw.step_off,
+                                         raw.entry_off, raw.entry_struct)]
+            if prof:
+                assert raw.family_ms["expand_fast"] > 0 and raw.family_launches["combine"] == raw.iterations
+            if ref is None:
+                ref = cur
+            else:
+                assert all((a == b).all() for a, b in zip(ref, cur)), (lanes, loop, prof)
+            raw.close()
+    finally:
+        ctx.set_option("lanes", 0); ctx.set_option("loop", 0); ctx.set_option("profile", 0)
+
+
+def test_multi_device_entry_matches_single(ctx, oracle):
+    """rafft_fold_batch_multi (one process, one host thread + stream per device): identical arrays to the
+    single-device call on every GPU count the box has; with one GPU the entry is exercised with one context"""
+    import torch
+    from rafft_b200 import rafft as R
+    seqs = config_batch("cfg2", 900)
+    offs = np.zeros(len(seqs) + 1, dtype=np.int64)
+    np.cumsum([len(s) for s in seqs], out=offs[1:])
+    sb, prm = "".join(seqs).encode(), R.make_params(100, 20, 1000, traj=True)
+    one = ctx.fold_raw(sb, offs, prm)
+    ref = [np.array(a) for a in (one.status, one.struct_off, one.energy, one.db_off, one.db, one.step_off,
+                                 one.entry_off, one.entry_struct, one.counters[:, :10])]
+    ndev = torch.cuda.device_count()
+    for nd in sorted({1, min(2, ndev), ndev}):
+        raw = R.fold_raw_multi([R.get_context(d) for d in range(nd)], sb, offs, prm)
+        cur = [np.array(a) for a in (raw.status, raw.struct_off, raw.energy, raw.db_off, raw.db, raw.step_off,
+                                     raw.entry_off, raw.entry_struct, raw.counters[:, :10])]
+        assert all(a.shape == b.shape and (a == b).all() for a, b in zip(ref, cur)), nd
+        raw.close()
+    got = R.fold_batch(seqs[:40], 100, 20, 1000, traj=True, devices=list(range(ndev)))
+    want, _ = oracle.fold_batch(seqs[:40], 100, 20, 1000)
+    assert [[[(s.str_struct, s.energy_dcal) for s in st] for st in tr] for _, tr in got] == want
 
 
 def test_random_parameters_vs_oracle(ctx, oracle):
@@ -260,11 +324,8 @@ def test_cfg3_full_batch_properties(ctx):
 
 
 def test_cfg4_3000nt_vs_oracle(ctx, oracle):
-    "configs[3] parameters (-n 200 -ms 200) on 3,000-nt inputs: bit-exact against the oracle"
-    seqs = [splitmix_seq(3000 + k, 3000) for k in range(2)]
-    got, _ = gpu_steps(ctx, seqs, nb_mode=200, max_stack=200)
-    want = oracle.fold_batch(seqs, 200, 200, 1000)[0]
-    assert got == want
+    "configs[3] parameters (-n 200 -ms 200) on eight 3,000-nt inputs: whole trajectories bit-exact against the oracle"
+    fold_and_check(ctx, oracle, [splitmix_seq(3000 + k, 3000) for k in range(8)], 200, 200)
 
 
 def test_cfg5_fold_then_kinetics(ctx, oracle):
