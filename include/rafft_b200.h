@@ -193,6 +193,9 @@ int rafft_set_option(rafft_ctx *ctx, const char *name, int64_t value);
  * kernels are measured against, bench.py roofline) and of an IADD3/LOP3 mix.  ~10 ms. */
 int rafft_int_peak(rafft_ctx *ctx, double *issue_warp_inst_per_s, double *mix_warp_inst_per_s);
 
+/* CUDA devices usable by rafft_create (0 without a driver / GPU). */
+int rafft_device_count(void);
+
 /* Library/build identification, e.g. "rafft_b200 0.1 sm_100a". */
 const char *rafft_version(void);
 

@@ -19,7 +19,7 @@ CNT_N = len(COUNTER_NAMES)
 EXPORTS = ("rafft_version", "rafft_default_energy_params", "rafft_create", "rafft_destroy",
            "rafft_last_error", "rafft_fold_batch", "rafft_fold_batch_device", "rafft_result_free",
            "rafft_eval_structures", "rafft_kin_graph", "rafft_bp_distance_matrix",
-           "rafft_fold_batch_multi", "rafft_set_option", "rafft_int_peak", "rafft_plan_ranges")
+           "rafft_fold_batch_multi", "rafft_set_option", "rafft_int_peak", "rafft_plan_ranges", "rafft_device_count")
 
 
 class EnergyParams(C.Structure):
@@ -117,6 +117,7 @@ def lib():
     L.rafft_fold_batch_multi.restype = C.c_int
     L.rafft_plan_ranges.argtypes = [C.POINTER(C.c_int64), C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32)]
     L.rafft_plan_ranges.restype = C.c_int
+    L.rafft_device_count.restype = C.c_int
     L.rafft_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
     L.rafft_set_option.restype = C.c_int
     L.rafft_int_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]

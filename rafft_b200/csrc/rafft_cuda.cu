@@ -307,10 +307,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_expand_fast(RF_WAVE_PARAM) {
 typedef void (*fast_kernel_t)(const WaveCtx);
 struct FastShape { int threads, blocks; fast_kernel_t fn; };
 static const FastShape g_fast_shapes[] = {
-    {512, 1, k_expand_fast<512, 1>}, {256, 2, k_expand_fast<256, 2>}, {256, 3, k_expand_fast<256, 3>},
-    {128, 4, k_expand_fast<128, 4>}, {128, 6, k_expand_fast<128, 6>}, {384, 2, k_expand_fast<384, 2>},
-    {768, 1, k_expand_fast<768, 1>}, {128, 5, k_expand_fast<128, 5>}, {64, 8, k_expand_fast<64, 8>},
-    {64, 12, k_expand_fast<64, 12>}};
+    {128, 6, k_expand_fast<128, 6>}, {256, 2, k_expand_fast<256, 2>}, {256, 3, k_expand_fast<256, 3>},
+    {256, 4, k_expand_fast<256, 4>}};
 
 /* One block.  Ordered offsets: struct_off/db_off/step_off (n+1 each) and the per-sequence
  * base of its entries, ent_base (n+1); totals[0..3] = structures, db bytes, steps, entries. */
@@ -566,6 +564,7 @@ struct rafft_ctx {
   int lanes = 0;            /* 0 automatic, 1..RF_MAX_LANES forced */
   int profile = 0;          /* per-kernel-family CUDA events (stepwise loop, one lane) */
   int persist = 1;          /* blocks per SM of the persistent block-scope kernels = occupancy * persist */
+  int lane_split = 50;      /* per cent of the estimated cost that goes to lane 0 when a call runs two lanes */
   int64_t mem_budget = 0;   /* bytes this context may use for arenas + scratch */
   double traj_ratio = 5.0;  /* structures per (sequence x max_stack) of the last traj = 1 call */
   uint32_t gen0 = 0;
@@ -661,6 +660,12 @@ extern "C" {
 
 const char *rafft_version(void) { return "rafft_b200 0.2 sm_100a"; }
 
+int rafft_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { (void)cudaGetLastError(); return 0; }
+  return n;
+}
+
 void rafft_default_energy_params(rafft_energy_params *ep) {
   if (ep) default_energy_params(ep);
 }
@@ -750,6 +755,8 @@ int rafft_create(rafft_ctx **out, int cuda_device, const rafft_energy_params *ep
     if (s) { int v = atoi(s); if (v >= 0 && v <= RF_MAX_LANES) ctx->lanes = v; }
     s = getenv("RAFFT_PROFILE");
     if (s) ctx->profile = atoi(s) != 0;
+    s = getenv("RAFFT_LANE_SPLIT");
+    if (s) { int v = atoi(s); if (v >= 5 && v <= 95) ctx->lane_split = v; }
     s = getenv("RAFFT_PERSIST");
     if (s) { int v = atoi(s); if (v >= 1 && v <= 8) ctx->persist = v; }
     return RAFFT_OK;
@@ -772,6 +779,7 @@ int rafft_set_option(rafft_ctx *ctx, const char *name, int64_t value) {
   else if (k == "loop" && (value == 0 || value == 1)) ctx->loop_mode = (int)value;
   else if (k == "max_wave" && value >= 0) ctx->max_wave = value;
   else if (k == "persist" && value >= 1 && value <= 8) ctx->persist = (int)value;
+  else if (k == "lane_split" && value >= 5 && value <= 95) ctx->lane_split = (int)value;
   else { ctx->err = "rafft_set_option: unknown option or value out of range: " + k; return RAFFT_ERR_ARG; }
   return RAFFT_OK;
 }
@@ -1460,11 +1468,11 @@ static int fold_job(rafft_ctx *const *ctxs, int n_ctx, const int *dev_lo, const 
     if (want == 0) want = (nt * F.max_stack >= (int64_t)24 << 20 && hi - lo >= 512) ? 2 : 1;
     if (ctxs[d]->profile || hi - lo < 2) want = 1;
     int cut = hi;
-    if (want == 2) { /* equal estimated cost on both sides */
+    if (want == 2) { /* lane 0 takes lane_split per cent of the estimated cost */
       double tot = 0, run = 0;
       for (int i = lo; i < hi; i++) tot += seq_cost(h_offs[i + 1] - h_offs[i], F.max_stack);
       cut = lo;
-      while (cut < hi - 1 && run < 0.5 * tot) { run += seq_cost(h_offs[cut + 1] - h_offs[cut], F.max_stack); cut++; }
+      while (cut < hi - 1 && run < 0.01 * ctxs[d]->lane_split * tot) { run += seq_cost(h_offs[cut + 1] - h_offs[cut], F.max_stack); cut++; }
       if (cut <= lo || cut >= hi) { want = 1; cut = hi; }
     }
     for (int l = 0; l < want; l++) {

@@ -191,6 +191,11 @@ def make_params(nb_mode=100, max_stack=1, max_branch=100, min_hp=3, min_nrj=0.0,
 _contexts = {}
 
 
+def device_count():
+    "CUDA devices the library can use"
+    return int(N.lib().rafft_device_count())
+
+
 def get_context(device=0):
     "process-wide context of a device, created on first use"
     ctx = _contexts.get(device)
