@@ -77,6 +77,8 @@ enum {
   RAFFT_CNT_T0_NS,        /* device globaltimer when the fold of this sequence started ... */
   RAFFT_CNT_T1_NS,        /* ... and ended (diagnostics: schedule / tail analysis) */
   RAFFT_CNT_N_EVAL_EXPAND,/* the part of N_EVAL made by find_best_consecutives (rafft/rafft.py:98) */
+  RAFFT_CNT_TRIVIAL_NODES,/* unique loop regions that cannot hold a stem (one position, or a hairpin inside of
+                             <= min_hp + 1 positions): settled without an expansion */
   RAFFT_CNT_N
 };
 

@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(HERE, "librafft_b200.so")
 RAFFT_OK, RAFFT_ERR_ARG, RAFFT_ERR_SEQ, RAFFT_ERR_CUDA, RAFFT_ERR_CAPACITY = 0, 1, 2, 3, 4
 MAX_SPECIAL = 64
 COUNTER_NAMES = ("steps", "node_exp", "w_corr", "w_scan", "n_eval", "uniq_nodes", "uniq_w_corr",
-                 "uniq_w_scan", "combos", "node_pos", "t0_ns", "t1_ns", "n_eval_expand")
+                 "uniq_w_scan", "combos", "node_pos", "t0_ns", "t1_ns", "n_eval_expand", "trivial_nodes")
 CNT_N = len(COUNTER_NAMES)
 
 # every symbol include/rafft_b200.h declares (tests check the library exports all of them)

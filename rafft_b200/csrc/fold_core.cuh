@@ -140,7 +140,7 @@ struct OutBuf {
 
 enum { CNT_STEPS = 0, CNT_NODE_EXP, CNT_W_CORR, CNT_W_SCAN, CNT_N_EVAL, CNT_UNIQ_NODES,
        CNT_UNIQ_W_CORR, CNT_UNIQ_W_SCAN, CNT_COMBOS, CNT_NODE_POS, CNT_T0_NS, CNT_T1_NS, CNT_N_EVAL_EXPAND,
-       CNT_N };
+       CNT_TRIVIAL_NODES, CNT_N };
 
 enum { ST_OK = 0, ST_ERR_SEQ = 2, ST_ERR_CAPACITY = 4 };
 
@@ -331,8 +331,11 @@ RF_NOINLINE int e_hairpin(const EnergyView &ev, int i, int j) {
   if (u < 3) return e;
   int t = pair_type(ev.s[i], ev.s[j]);
   if (u == 3 || u == 4 || u == 6) {
-    uint32_t key = 0;
-    for (int k = i; k <= j; k++) key = (key << 2) | ev.s[k];
+    /* 2 bits per base, first base highest: independent loads instead of a loop of dependent ones */
+    const uint8_t *q = ev.s + i;
+    uint32_t key = ((uint32_t)q[0] << 8) | ((uint32_t)q[1] << 6) | ((uint32_t)q[2] << 4) | ((uint32_t)q[3] << 2) | (uint32_t)q[4];
+    if (u >= 4) key = (key << 2) | (uint32_t)q[5];
+    if (u == 6) key = (key << 4) | ((uint32_t)q[6] << 2) | (uint32_t)q[7];
     if (u == 4) {
       if ((P->tetra_bm[key >> 5] >> (key & 31)) & 1)
         for (int k = 0; k < P->n_tetra; k++)
@@ -1329,11 +1332,23 @@ struct Fold {
     while ((32 << k2) < 2 * (nd).lv - 1) k2++;                                                \
     cls = 2 * k2 + (2 * (nd).lv - 1 > (24 << k2) ? 1 : 0);                                    \
   }
+    /* A region that cannot hold a stem needs no expansion: a single position, or the inside of a
+     * hairpin loop too short for a pair to span min_hp positions (pos[j] - pos[i] = j - i there,
+     * rafft.py:78).  The reference still ranks and scans its lags; those counts have a closed form
+     * when every lag is ranked. */
     RF_PAR_BEGIN(x, n_new_nodes)
-      const NodeRec &nd = A.node[from + x];
+      NodeRec &nd = A.node[from + x];
       if (nd.nht_slot >= 0 && nd.cand_n == -1) {
-        RF_GATHER_CLASS(nd, cls)
-        Exec::atomic_add(&sh->qcnt[cls], 1);
+        const int nlag0 = 2 * nd.lv - 1;
+        if ((nd.lv == 1 || (nd.br_n == 0 && nd.lv <= prm.min_hp + 1)) && nlag0 <= prm.nb_mode) {
+          long long ws = 0;
+          for (int d = 1; d <= nd.lv; d++) ws += ((d + 1) >> 1) * (d < nd.lv ? 2 : 1);
+          nd.cand_off = 0; nd.cand_n = 0; nd.n_ranked = nlag0; nd.n_pos = 0; nd.w_scan = ws;
+          count(CNT_TRIVIAL_NODES, 1);
+        } else {
+          RF_GATHER_CLASS(nd, cls)
+          Exec::atomic_add(&sh->qcnt[cls], 1);
+        }
       }
     RF_PAR_END
     RF_SINGLE_BEGIN

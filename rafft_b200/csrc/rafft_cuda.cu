@@ -51,7 +51,9 @@ struct LoopCtl {
   int32_t iters;                     /* folding iterations run */
   int32_t seen_gen;                  /* generation tag of this fold's `seen` entries */
   int32_t work[4];                   /* dynamic cursors of gather / combine / select / materialise */
-  int32_t pad_[28];
+  int32_t fast_total[RF_FAST_LISTS]; /* regions per work list over the whole fold (diagnostics) */
+  int32_t generic_total;
+  int32_t pad_[15];
 };
 
 /* Everything the phase kernels of one wave need (kernel parameter, constant bank).
@@ -125,9 +127,10 @@ struct BlockBind {
  * change from fold to fold while the graph of the loop is cached) */
 __global__ void k_ctl_reset(LoopCtl *ctl, int nw, int gen) {
   const int t = threadIdx.x;
-  if (t < RF_FAST_LISTS) { ctl->n_fast[t] = 0; ctl->fast_next[t] = 0; }
+  if (t < RF_FAST_LISTS) { ctl->n_fast[t] = 0; ctl->fast_next[t] = 0; ctl->fast_total[t] = 0; }
   if (t < 4) ctl->work[t] = 0;
   if (t == 0) {
+    ctl->generic_total = 0;
     ctl->n_tasks = 0; ctl->n_next = 0; ctl->n_cur = nw; ctl->parity = 0; ctl->iters = 0; ctl->seen_gen = gen;
   }
 }
@@ -196,9 +199,10 @@ __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_materialise(RF_WAVE_PA
  * (stream mode) */
 __global__ void k_advance(LoopCtl *ctl, int32_t *h_prog, cudaGraphConditionalHandle handle, int use_handle) {
   const int t = threadIdx.x;
-  if (t < RF_FAST_LISTS) { ctl->n_fast[t] = 0; ctl->fast_next[t] = 0; }
+  if (t < RF_FAST_LISTS) { ctl->fast_total[t] += ctl->n_fast[t]; ctl->n_fast[t] = 0; ctl->fast_next[t] = 0; }
   if (t < 4) ctl->work[t] = 0;
   if (t == 0) {
+    ctl->generic_total += ctl->n_tasks;
     const int n = ctl->n_next;
     ctl->n_cur = n; ctl->n_next = 0; ctl->parity ^= 1; ctl->n_tasks = 0;
     const int it = ++ctl->iters;
@@ -1281,6 +1285,14 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
       T.iters += iters;
       T.launches += 2 + (int64_t)iters * per_iter;
       T.d2h += 4;
+      if (dbg) { /* regions per size class (work lists of the shared-memory expansion, lower/upper half of each class) */
+        LoopCtl hc;
+        cudaMemcpyAsync(&hc, ctl, sizeof hc, cudaMemcpyDeviceToHost, ln.stream);
+        cudaStreamSynchronize(ln.stream);
+        fprintf(stderr, "[rafft] lane %d regions per list (lags <= 24,32,48,64,...):", k);
+        for (int q = 0; q < RF_FAST_LISTS; q++) fprintf(stderr, " %d", hc.fast_total[q]);
+        fprintf(stderr, "; generic %d\n", hc.generic_total);
+      }
       if (dbg) { /* high-water marks of the arena pieces against their capacities */
         std::vector<SeqState> hs((size_t)nw);
         cudaMemcpyAsync(hs.data(), ln.states.p, sizeof(SeqState) * (size_t)nw, cudaMemcpyDeviceToHost, ln.stream);
@@ -1465,7 +1477,11 @@ static int fold_job(rafft_ctx *const *ctxs, int n_ctx, const int *dev_lo, const 
     const int lo = dev_lo[d], hi = dev_lo[d + 1];
     int64_t nt = h_offs[hi] - h_offs[lo];
     int want = ctxs[d]->lanes;
-    if (want == 0) want = (nt * F.max_stack >= (int64_t)24 << 20 && hi - lo >= 512) ? 2 : 1;
+    /* measured on B200 (profiles/r02_lanes.md): two half-batches double the number of kernel tails and
+     * lose more than the overlapped result copy gains, so one lane is the default; RAFFT_LANES=2 /
+     * rafft_set_option("lanes", 2) turn the overlap on */
+    if (want == 0) want = 1;
+    (void)nt;
     if (ctxs[d]->profile || hi - lo < 2) want = 1;
     int cut = hi;
     if (want == 2) { /* lane 0 takes lane_split per cent of the estimated cost */

@@ -19,7 +19,7 @@ for l in sys.stdin:
     key = f
     if f == 'expand_fast.cuh': key = fn(ln)
     elif f == 'fold_core.cuh':
-        key = 'pair_fp/mix64' if 278 <= ln <= 292 else 'pair_type' if 292 < ln <= 299 else 'e_hairpin' if 306 <= ln <= 335 else 'e_interior' if 336 <= ln <= 373 else 'ml/ext stem' if 374 <= ln <= 392 else 'fold_core %d' % ln
+        key = "pair_fp/mix64" if 297 <= ln <= 307 else "pair_type" if 308 <= ln <= 314 else "e_hairpin" if 323 <= ln <= 352 else "e_interior" if 354 <= ln <= 390 else "ml/ext stem" if 392 <= ln <= 406 else 'fold_core %d' % ln
     elif f == 'rafft_cuda.cu': key = 'kernel body (barriers, fetch)'
     a = agg.setdefault(key, [0, 0, 0]); a[0] += i; a[1] += s; a[2] += i * th
 for k, (i, s, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]): print('%-32s inst %6.2f%%  samples %6.2f%%  active threads %4.1f' % (k, i, s, t / max(i, 1e-9)))
