@@ -38,6 +38,7 @@ struct FastCfg {
   int32_t o_mask, o_pos, o_brcnt, o_lcode, o_pre, o_A; /* byte offsets in the warp slice */
   int32_t o_stem, o_ck, o_nb;                                  /* pieces of A after the ranking */
   int32_t o_wst;                                               /* 4 ints of warp state */
+  int32_t o_rank; /* rank of every lag (uint16), behind o_nb inside A; dead once the scan order is built */
 };
 
 #ifndef __CUDACC_RTC__
@@ -67,12 +68,13 @@ inline bool build_fast_cfg(FastCfg &fc, int L_max, const FoldParams &F) {
   fc.o_pre = carve(4 * 2 * (size_t)(fc.br_cap + 1));
   fc.o_wst = carve(16);
   size_t a_keys = 4 * (size_t)nk_cap;
-  size_t a_after = 4 * (size_t)nr + 4 * (size_t)ck_cap + 2 * (size_t)nr + 48;
+  size_t a_after = 4 * (size_t)nr + 4 * (size_t)ck_cap + 2 * (size_t)nr + 32 + 2 * (size_t)nk_cap;
   fc.o_A = carve(a_keys > a_after ? a_keys : a_after);
   fc.o_stem = fc.o_A;
   fc.o_ck = fc.o_stem + 4 * nr;
   fc.o_ck = (fc.o_ck + 15) / 16 * 16;
   fc.o_nb = fc.o_ck + 4 * ck_cap;
+  fc.o_rank = (fc.o_nb + 2 * nr + 15) / 16 * 16;
   fc.smem_per_warp = (int32_t)((off + 127) / 128 * 128);
   fc.enabled = 1;
   return true;
@@ -353,29 +355,14 @@ __device__ __forceinline__ void fast_p4(RF_FAST_ARGS) {
   RF_FAST_BIND
   uint32_t vreg[K];
   fast_sort_regs<K>(keys, vreg, lane);
-  __syncwarp(); /* the scan order below is written into the key buffer */
+  __syncwarp(); /* rank_of lies inside the key buffer */
   /* rank t = register t % K of lane t / K; the padding keys (0) sort behind every real lag */
-  /* Scan order of phase 5: the ranked lags by decreasing weighted pair count of the half
-   * anti-diagonal they scan (acc, recovered from the ranking key up to rounding) -- an estimate of
-   * the set bits the scan will walk.  Every lane scans one lag per round, so lanes of a round then
-   * carry nearly the same work and the incomplete last round holds the cheapest lags.  Results
-   * stay indexed by rank: the order is invisible outside. */
-  uint32_t *perm = (uint32_t *)(ws + fc.o_ck); /* (estimate << 18) | (lag << 8) | rank */
-  int nkc = 32;
-  while (nkc < nr) nkc <<= 1;
-  for (int x = nr + lane; x < nkc; x += 32) perm[x] = 0;
+  uint16_t *rank_of = (uint16_t *)(ws + fc.o_rank);
 #pragma unroll
   for (int q = 0; q < K; q++) {
     const int t = K * lane + q;
-    if (t < nr) {
-      const uint32_t pk = vreg[q] & ((1u << RF_FAST_LAGBITS) - 1);
-      const int pp = (int)pk;
-      const uint32_t d = (uint32_t)(pp < lv ? pp + 1 : 2 * lv - 1 - pp);
-      const uint32_t est = ((vreg[q] >> RF_FAST_LAGBITS) * d) >> RF_FAST_SHIFT;
-      perm[t] = (est << 18) | (pk << 8) | (uint32_t)t;
-    }
+    if (t < nlag) rank_of[vreg[q] & ((1u << RF_FAST_LAGBITS) - 1)] = (uint16_t)t;
   }
-  if (nr > 32) fast_sort_dispatch(perm, nkc, lane);
 }
 
 /* phase 5: per ranked lag the best consecutive stem (window_slide, rafft.py:36-83) over the set
@@ -388,12 +375,28 @@ __device__ __forceinline__ void fast_p5(RF_FAST_ARGS) {
    * constant bank inside the bit loop */
   const int hGC = __shfl_sync(FULL, __double2hiint(dGC), 0), hAU = __shfl_sync(FULL, __double2hiint(dAU), 0),
             hGU = __shfl_sync(FULL, __double2hiint(dGU), 0);
-  const uint32_t *perm = ck; /* scan order built by phase 4; ck is not used before phase 6 */
-  __syncwarp();
+  /* Scan order: the ranked lags by decreasing length of their anti-diagonal (p = lv-1, lv-2, lv,
+   * lv-3, lv+1, ...), compacted by ballot.  Every lane scans one lag per round; lanes of a
+   * round then carry nearly the same work and the incomplete last round holds the shortest
+   * lags.  Results stay indexed by rank, so the order is invisible outside. */
+  uint32_t *perm = ck; /* (lag << 16) | rank; ck is not used before phase 6 */
+  {
+    const uint16_t *rank_of = (const uint16_t *)(ws + fc.o_rank);
+    int n_perm = 0;
+    for (int k0 = 0; k0 < nlag && n_perm < nr; k0 += 32) {
+      const int k = k0 + lane;
+      const int p = (k & 1) ? lv - 1 - ((k + 1) >> 1) : lv - 1 + (k >> 1);
+      const int rk = k < nlag ? rank_of[p] : 0xffff;
+      const unsigned bal = __ballot_sync(FULL, rk < nr);
+      if (rk < nr) perm[n_perm + __popc(bal & ((1u << lane) - 1))] = ((uint32_t)p << 16) | (uint32_t)rk;
+      n_perm += __popc(bal);
+    }
+    __syncwarp();
+  }
   int w_scan = 0;
   for (int x = lane; x < nr; x += 32) {
     const uint32_t pr = perm[x];
-    const int p = (int)((pr >> 8) & ((1u << RF_FAST_LAGBITS) - 1)), r = (int)(pr & 0xffu);
+    const int p = (int)(pr >> 16), r = (int)(pr & 0xffffu);
     const int s = lv - 1 - p;
     const int i0 = p < lv ? 0 : p - lv + 1;
     const int d = p < lv ? p + 1 : 2 * lv - 1 - p;
