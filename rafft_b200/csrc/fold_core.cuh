@@ -529,6 +529,11 @@ struct TaskQueue {
   int32_t *n_fast;    /* RF_FAST_LISTS counters */
   int32_t fast_cap, fast_lv, fast_br;
   int32_t *fast_task; /* RF_FAST_LISTS lists of fast_cap tasks, 2 ints per task */
+  /* third list: regions of up to big_lv positions for the block-per-region expansion
+   * (expand_big.cuh); big_cap == 0 sends them to the first list */
+  int32_t *n_big;
+  int32_t big_cap, big_lv, big_br;
+  int32_t *big_task;
 };
 
 RF_HD size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
@@ -1331,6 +1336,8 @@ struct Fold {
     int k2 = 0;                                                                               \
     while ((32 << k2) < 2 * (nd).lv - 1) k2++;                                                \
     cls = 2 * k2 + (2 * (nd).lv - 1 > (24 << k2) ? 1 : 0);                                    \
+  } else if (Q.big_cap > 0 && (nd).lv <= Q.big_lv && (nd).br_n <= Q.big_br) {                 \
+    cls = RF_FAST_LISTS + 1;                                                                  \
   }
     /* A region that cannot hold a stem needs no expansion: a single position, or the inside of a
      * hairpin loop too short for a pair to span min_hp positions (pos[j] - pos[i] = j - i there,
@@ -1352,8 +1359,9 @@ struct Fold {
       }
     RF_PAR_END
     RF_SINGLE_BEGIN
-      for (int c = 0; c <= RF_FAST_LISTS; c++) {
-        if (sh->qcnt[c]) sh->qbase[c] = Exec::atomic_add(c < RF_FAST_LISTS ? Q.n_fast + c : Q.n_tasks, sh->qcnt[c]);
+      for (int c = 0; c <= RF_FAST_LISTS + 1; c++) {
+        if (sh->qcnt[c])
+          sh->qbase[c] = Exec::atomic_add(c < RF_FAST_LISTS ? Q.n_fast + c : c == RF_FAST_LISTS ? Q.n_tasks : Q.n_big, sh->qcnt[c]);
         sh->qcnt[c] = 0;
       }
     RF_SINGLE_END
@@ -1361,9 +1369,9 @@ struct Fold {
       NodeRec &nd = A.node[from + x];
       if (nd.nht_slot >= 0 && nd.cand_n == -1) {
         RF_GATHER_CLASS(nd, cls)
-        const bool fast = cls < RF_FAST_LISTS;
-        int32_t *list = fast ? Q.fast_task + 2 * (size_t)cls * (size_t)Q.fast_cap : Q.task;
-        const int cap = fast ? Q.fast_cap : Q.cap;
+        const bool fast = cls < RF_FAST_LISTS, big = cls > RF_FAST_LISTS;
+        int32_t *list = fast ? Q.fast_task + 2 * (size_t)cls * (size_t)Q.fast_cap : big ? Q.big_task : Q.task;
+        const int cap = fast ? Q.fast_cap : big ? Q.big_cap : Q.cap;
         const int at = sh->qbase[cls] + Exec::atomic_add(&sh->qcnt[cls], 1);
         if (at < cap) { list[2 * at] = Q.self; list[2 * at + 1] = from + x; nd.cand_n = -2; }
         else sh->expand_pending = 1; /* next round */

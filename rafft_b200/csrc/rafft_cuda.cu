@@ -31,6 +31,7 @@
 #include <vector>
 #include "host_common.h"
 #include "expand_fast.cuh"
+#include "expand_big.cuh"
 #include "kin_cuda.cuh"
 
 using namespace rafft;
@@ -53,7 +54,8 @@ struct LoopCtl {
   int32_t work[4];                   /* dynamic cursors of gather / combine / select / materialise */
   int32_t fast_total[RF_FAST_LISTS]; /* regions per work list over the whole fold (diagnostics) */
   int32_t generic_total;
-  int32_t pad_[15];
+  int32_t n_big, big_next, big_total; /* work list of the block-per-region expansion */
+  int32_t pad_[12];
 };
 
 /* Everything the phase kernels of one wave need (kernel parameter, constant bank).
@@ -74,6 +76,7 @@ struct WaveCtx {
   int32_t n;
   TaskQueue Q;
   FastCfg fast;
+  BigCfg big;
   LoopCtl *ctl;
   int32_t *alist;     /* two lists of acap wave slots: the sequences still folding */
   int32_t acap;
@@ -130,7 +133,7 @@ __global__ void k_ctl_reset(LoopCtl *ctl, int nw, int gen) {
   if (t < RF_FAST_LISTS) { ctl->n_fast[t] = 0; ctl->fast_next[t] = 0; ctl->fast_total[t] = 0; }
   if (t < 4) ctl->work[t] = 0;
   if (t == 0) {
-    ctl->generic_total = 0;
+    ctl->generic_total = 0; ctl->n_big = 0; ctl->big_next = 0; ctl->big_total = 0;
     ctl->n_tasks = 0; ctl->n_next = 0; ctl->n_cur = nw; ctl->parity = 0; ctl->iters = 0; ctl->seen_gen = gen;
   }
 }
@@ -203,6 +206,7 @@ __global__ void k_advance(LoopCtl *ctl, int32_t *h_prog, cudaGraphConditionalHan
   if (t < 4) ctl->work[t] = 0;
   if (t == 0) {
     ctl->generic_total += ctl->n_tasks;
+    ctl->big_total += ctl->n_big; ctl->n_big = 0; ctl->big_next = 0;
     const int n = ctl->n_next;
     ctl->n_cur = n; ctl->n_next = 0; ctl->parity ^= 1; ctl->n_tasks = 0;
     const int it = ++ctl->iters;
@@ -305,6 +309,22 @@ __global__ void __launch_bounds__(THREADS, MINB) k_expand_fast(RF_WAVE_PARAM) {
   for (int sub = 1; sub >= 0; sub--) fast_class<2>(c, 2 + sub, ws, &s_base);
 #pragma unroll 1
   for (int sub = 1; sub >= 0; sub--) fast_class<1>(c, sub, ws, &s_base);
+}
+
+/* block-per-region expansion of long regions (expand_big.cuh): persistent blocks pull regions */
+__global__ void __launch_bounds__(RF_BIG_THREADS, 2) k_expand_big(RF_WAVE_PARAM) {
+  extern __shared__ __align__(16) char big_smem[];
+  __shared__ int s_task;
+  const int nt = min(c.ctl->n_big, c.Q.big_cap);
+  for (;;) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_task = atomicAdd(&c.ctl->big_next, 1);
+    __syncthreads();
+    const int t = s_task;
+    if (t >= nt) break;
+    const int j = c.Q.big_task[2 * t], v = c.Q.big_task[2 * t + 1];
+    big_expand(c.E, c.prm, c.caps, c.big, c.arenas + (size_t)j * (size_t)c.caps.arena_bytes, c.aoff, c.states + j, v, big_smem);
+  }
 }
 
 /* launch shapes of k_expand_fast: (threads per block, blocks per SM) */
@@ -537,7 +557,7 @@ struct Lane {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev1 = nullptr;
   cudaEvent_t pev[RF_PROF_EVENTS] = {};
-  DevBuf arenas, order, idx, big, ordered, scan, states, tasks, ftasks, scratch, ctl, alist;
+  DevBuf arenas, order, idx, big, ordered, scan, states, tasks, ftasks, btasks, scratch, ctl, alist;
   int64_t *h_small = nullptr;  /* pinned + mapped: [0..7] totals/cursors, [8..] loop progress words */
   uint64_t arena_sig = 0;      /* layout of the arenas whose hash tables are known to be empty */
   bool arena_dirty = true;
@@ -564,6 +584,7 @@ struct rafft_ctx {
   int64_t max_tasks = 0;    /* capacity of the region work list (0 = automatic) */
   int fast_shape = 2;       /* index into g_fast_shapes (RAFFT_FAST_SHAPE) */
   int use_fast = 1;         /* shared-memory expansion for small regions (RAFFT_FAST=0 disables) */
+  int use_big = 1;          /* block-per-region shared-memory expansion for long regions (RAFFT_BIG=0 disables) */
   int loop_mode = 0;        /* 0 graph WHILE node, 1 stream launches with bounded look-ahead */
   int lanes = 0;            /* 0 automatic, 1..RF_MAX_LANES forced */
   int profile = 0;          /* per-kernel-family CUDA events (stepwise loop, one lane) */
@@ -646,7 +667,7 @@ static int host_block_get(rafft_ctx *ctx, size_t bytes, HostBlock *hb) {
 
 static void lane_destroy(Lane &ln) {
   DevBuf *bufs[] = {&ln.arenas, &ln.order, &ln.idx, &ln.big, &ln.ordered, &ln.scan, &ln.states,
-                    &ln.tasks, &ln.ftasks, &ln.scratch, &ln.ctl, &ln.alist};
+                    &ln.tasks, &ln.ftasks, &ln.btasks, &ln.scratch, &ln.ctl, &ln.alist};
   for (DevBuf *b : bufs)
     if (b->p) cudaFree(b->p);
   for (GraphSlot &g : ln.graphs) {
@@ -751,6 +772,8 @@ int rafft_create(rafft_ctx **out, int cuda_device, const rafft_energy_params *ep
     if (s) { int v = atoi(s); if (v >= 0 && v < (int)(sizeof g_fast_shapes / sizeof g_fast_shapes[0])) ctx->fast_shape = v; }
     s = getenv("RAFFT_FAST");
     if (s) ctx->use_fast = atoi(s) != 0;
+    s = getenv("RAFFT_BIG");
+    if (s) ctx->use_big = atoi(s) != 0;
     s = getenv("RAFFT_MAX_TASKS");
     if (s) { long v = atol(s); if (v >= 1) ctx->max_tasks = v; }
     s = getenv("RAFFT_LOOP"); /* graph (default) | stream */
@@ -908,7 +931,9 @@ struct WavePlan {
   int g_gather = 0, g_combine = 0, g_select = 0, g_mat = 0, g_fast = 0, egrid = 0;
   size_t stage_bytes = 0, fast_smem = 0;
   const FastShape *fsh = nullptr;
-  bool use_fast = false, any_generic = false;
+  bool use_fast = false, any_generic = false, use_big = false;
+  int g_big = 0;
+  size_t big_smem = 0;
 };
 
 /* the kernels of one folding iteration; fam_ev != nullptr: a CUDA event before every kernel family
@@ -923,6 +948,7 @@ static void emit_iteration(Emit &E, WavePlan &P, cudaGraphConditionalHandle hand
   E.kernel((const void *)k_gather, dim3(P.g_gather), dim3(P.T_gather), 0, a_wc);
   mark();
   if (P.use_fast) E.kernel((const void *)P.fsh->fn, dim3(P.g_fast), dim3(P.fsh->threads), P.fast_smem, a_wc);
+  if (P.use_big) E.kernel((const void *)k_expand_big, dim3(P.g_big), dim3(RF_BIG_THREADS), P.big_smem, a_wc);
   mark();
   if (P.any_generic) {
     E.kernel((const void *)k_expand<1>, dim3(P.egrid), dim3(128), 0, a_wc);
@@ -949,7 +975,7 @@ static void emit_iteration(Emit &E, WavePlan &P, cudaGraphConditionalHandle hand
  * `why`) when the graph cannot be built; the caller then drives the same kernels from the stream. */
 static cudaGraphExec_t wave_graph(Lane &ln, WavePlan &P, std::string &why) {
   /* key: every kernel argument and launch dimension */
-  std::vector<unsigned char> key(sizeof(WaveCtx) + 16 * sizeof(int) + 2 * sizeof(size_t));
+  std::vector<unsigned char> key(sizeof(WaveCtx) + 16 * sizeof(int) + 4 * sizeof(size_t));
   {
     unsigned char *k = key.data();
     memcpy(k, &P.wc, sizeof(WaveCtx)); k += sizeof(WaveCtx);
@@ -958,7 +984,10 @@ static cudaGraphExec_t wave_graph(Lane &ln, WavePlan &P, std::string &why) {
                           P.fsh ? P.fsh->threads : 0};
     memcpy(k, dims, sizeof dims); k += sizeof dims;
     memcpy(k, &P.stage_bytes, sizeof(size_t)); k += sizeof(size_t);
-    memcpy(k, &P.fast_smem, sizeof(size_t));
+    memcpy(k, &P.fast_smem, sizeof(size_t)); k += sizeof(size_t);
+    memcpy(k, &P.big_smem, sizeof(size_t)); k += sizeof(size_t);
+    const size_t bigdims = (size_t)P.g_big * 2 + (P.use_big ? 1 : 0);
+    memcpy(k, &bigdims, sizeof(size_t));
   }
   GraphSlot *victim = &ln.graphs[0];
   for (GraphSlot &g : ln.graphs) {
@@ -1109,7 +1138,14 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
     } else {
       memset(&fastcfg, 0, sizeof fastcfg);
     }
-    if (ctx->max_tasks > 0) { qcap = std::min<int64_t>(qcap, ctx->max_tasks); fcap = std::min<int64_t>(fcap, ctx->max_tasks); }
+    /* regions beyond the warp-per-region path take the block-per-region one (expand_big.cuh) */
+    BigCfg bigcfg;
+    int64_t bcap = 0;
+    if (ctx->use_big && fcap > 0 && Lr > fastcfg.L_cap && build_big_cfg(bigcfg, Lr, F))
+      bcap = wave * std::min<int64_t>(2 * (int64_t)F.max_stack + 8, 512);
+    else
+      memset(&bigcfg, 0, sizeof bigcfg);
+    if (ctx->max_tasks > 0) { qcap = std::min<int64_t>(qcap, ctx->max_tasks); fcap = std::min<int64_t>(fcap, ctx->max_tasks); bcap = std::min<int64_t>(bcap, ctx->max_tasks); }
     {
       /* The unique-loop tables at the head of every arena must be empty before a run; a run leaves
        * them empty again, so they are zeroed only when the buffer or its layout changes (or after
@@ -1134,6 +1170,7 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
     if (int rc = dev_reserve_s(ln.err, ln.tasks, sizeof(int32_t) * 2 * (size_t)qcap)) return rc;
     if (int rc = dev_reserve_s(ln.err, ln.ftasks, sizeof(int32_t) * 2 * RF_FAST_LISTS * (size_t)(fcap + 1))) return rc;
     if (int rc = dev_reserve_s(ln.err, ln.scratch, (size_t)qcap * (size_t)caps.wscratch_bytes)) return rc;
+    if (int rc = dev_reserve_s(ln.err, ln.btasks, sizeof(int32_t) * 2 * (size_t)(bcap + 1))) return rc;
     if (int rc = dev_reserve_s(ln.err, ln.alist, sizeof(int32_t) * 2 * (size_t)wave)) return rc;
     WaveCtx &wc = P.wc;
     memset(&wc, 0, sizeof wc);
@@ -1150,11 +1187,18 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
     wc.Q.n_fast = ctl->n_fast; wc.Q.fast_cap = (int32_t)fcap; wc.Q.fast_task = (int32_t *)ln.ftasks.p;
     wc.Q.fast_lv = fastcfg.L_cap; wc.Q.fast_br = fastcfg.br_cap;
     wc.fast = fastcfg;
+    wc.Q.n_big = &ctl->n_big; wc.Q.big_cap = (int32_t)bcap; wc.Q.big_task = (int32_t *)ln.btasks.p;
+    wc.Q.big_lv = bigcfg.L_cap; wc.Q.big_br = bigcfg.br_cap;
+    wc.big = bigcfg;
+    P.use_big = bcap > 0;
+    P.big_smem = (size_t)bigcfg.smem_bytes;
+    P.g_big = ctx->sm_count * 2;
+    if (P.use_big) LCK(cudaFuncSetAttribute(k_expand_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P.big_smem));
     P.fsh = &g_fast_shapes[ctx->fast_shape];
     P.fast_smem = (size_t)(P.fsh->threads / 32) * (size_t)fastcfg.smem_per_warp;
     P.use_fast = fcap > 0;
     /* a branch of a loop covers at least min_hp + 2 positions */
-    P.any_generic = fcap == 0 || Lr > fastcfg.L_cap || Lr / (F.min_hp + 2) > fastcfg.br_cap;
+    P.any_generic = fcap == 0 || Lr > (bcap > 0 ? bigcfg.L_cap : fastcfg.L_cap) || Lr / (F.min_hp + 2) > fastcfg.br_cap;
     wc.out = O;
     CombineStage cs_probe;
     P.stage_bytes = stage_carve(cs_probe, nullptr, caps.chunk_cap, F.max_stack);
@@ -1211,7 +1255,7 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
       h_prog[0] = 0; h_prog[1] = 0; /* the lane's stream is idle here: no kernel writes them now */
       k_ctl_reset<<<1, 64, 0, ln.stream>>>(ctl, nw, (int)ln.seen_gen);
       T.launches++;
-      const int per_iter = 1 + (P.use_fast ? 1 : 0) + (P.any_generic ? 5 : 0) + 3 + 1;
+      const int per_iter = 1 + (P.use_fast ? 1 : 0) + (P.use_big ? 1 : 0) + (P.any_generic ? 5 : 0) + 3 + 1;
       bool done = false;
       if (!profile && ctx->loop_mode == 0) {
         std::string why;
@@ -1291,7 +1335,7 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
         cudaStreamSynchronize(ln.stream);
         fprintf(stderr, "[rafft] lane %d regions per list (lags <= 24,32,48,64,...):", k);
         for (int q = 0; q < RF_FAST_LISTS; q++) fprintf(stderr, " %d", hc.fast_total[q]);
-        fprintf(stderr, "; generic %d\n", hc.generic_total);
+        fprintf(stderr, "; big %d; generic %d\n", hc.big_total, hc.generic_total);
       }
       if (dbg) { /* high-water marks of the arena pieces against their capacities */
         std::vector<SeqState> hs((size_t)nw);

@@ -52,6 +52,7 @@ int emu_fold(const rafft_energy_params *ep_in, const char *seq, int L, const raf
   std::vector<char> scratch((size_t)caps.wscratch_bytes);
   f.Q.n_tasks = &n_tasks; f.Q.cap = qcap; f.Q.task = tasks.data(); f.Q.scratch = scratch.data(); f.Q.self = 0;
   f.Q.n_fast = nullptr; f.Q.fast_cap = 0; f.Q.fast_lv = 0; f.Q.fast_br = 0; f.Q.fast_task = nullptr; /* CUDA-only path */
+  f.Q.n_big = nullptr; f.Q.big_cap = 0; f.Q.big_lv = 0; f.Q.big_br = 0; f.Q.big_task = nullptr;
   CombineStage probe;
   std::vector<char> stage(stage_carve(probe, nullptr, caps.chunk_cap, F.max_stack) + 64);
   stage_carve(f.cs, (char *)(((uintptr_t)stage.data() + 15) & ~(uintptr_t)15), caps.chunk_cap, F.max_stack);
