@@ -506,17 +506,9 @@ __device__ __forceinline__ void fast_p7(RF_FAST_ARGS) {
         const int mip = ij >> 16, mjp = ij & 0xffff, nb = r_nb[r];
         Cand &c = cand[at];
         c.dE = (int32_t)(key >> 8) - 0x800000;
-        c.mip = (uint16_t)mip; c.mjp = (uint16_t)mjp; c.nb = (uint16_t)nb; c.rank = (uint16_t)r;
-        c.pad_ = 0;
         ckid[at].inner_id = (mjp - mip > 1) ? -1 : -2;                       /* rafft.py:130 */
         ckid[at].outer_id = (mip - (nb - 1) > 0 || mjp + nb < lv) ? -1 : -2; /* rafft.py:141 */
-        uint64_t flo = 0, fhi = 0;
-        for (int k = 0; k < nb; k++) {
-          uint64_t l1, h1;
-          pair_fp(pos[mip - k], pos[mjp + k], l1, h1);
-          flo += l1; fhi += h1;
-        }
-        c.fp_lo = flo; c.fp_hi = fhi;
+        cand_geometry(c, pos, brcnt, mip, mjp, nb);
       }
     }
   }

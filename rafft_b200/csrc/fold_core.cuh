@@ -97,10 +97,18 @@ struct NodeRec {
  * The child loop ids, which only the selected children need, live in Arena::ckid. */
 struct Cand {
   int32_t dE;
-  uint16_t mip, mjp, nb, rank;
-  int32_t pad_;
+  uint16_t mip, mjp, nb;      /* innermost pair (local indices of the region) and pairs of the stem */
+  uint16_t hh;                /* branches of the region's loop before mip | before mjp << 8 */
+  uint32_t geo;               /* original position of the innermost pair: i | j << 12, bit 24 set when
+                                 the stem is contiguous in original coordinates (pair k = (i - k, j + k))
+                                 and both branch counts fit hh; 0: geometry through the loop record */
   uint64_t fp_lo, fp_hi;      /* sum of pair fingerprints of the stem */
 };
+#define RF_GEO_OK (1u << 24)
+/* geometry + fingerprint of a stem; pos[t]: original position of local index t, brcnt[t]: branches
+ * before it */
+template <class PosT, class BrT>
+RF_FN void cand_geometry(Cand &c, const PosT *pos, const BrT *brcnt, int mip, int mjp, int nb);
 static_assert(sizeof(Cand) == 32, "Cand is one sector");
 struct CandKid {
   int32_t inner_id, outer_id; /* -1 unresolved, -2 no such node, -3 being created */
@@ -310,6 +318,25 @@ RF_FN int pair_type(int a, int b) {
   const uint64_t T = (5ULL << 12) | (1ULL << 24) | (2ULL << 36) | (3ULL << 44) | (6ULL << 48) |
                      (4ULL << 56);
   return (int)((T >> (4 * (a * 4 + b))) & 15) - 1;
+}
+
+template <class PosT, class BrT>
+RF_FN void cand_geometry(Cand &c, const PosT *pos, const BrT *brcnt, int mip, int mjp, int nb) {
+  const int oi = (int)pos[mip], oj = (int)pos[mjp];
+  const int h1 = (int)brcnt[mip], h2 = (int)brcnt[mjp];
+  bool plain = h1 < 256 && h2 < 256;
+  uint64_t flo = 0, fhi = 0;
+  for (int k = 0; k < nb; k++) {
+    const int a = (int)pos[mip - k], b = (int)pos[mjp + k];
+    plain = plain && a == oi - k && b == oj + k;
+    uint64_t l1, h1_;
+    pair_fp(a, b, l1, h1_);
+    flo += l1; fhi += h1_;
+  }
+  c.mip = (uint16_t)mip; c.mjp = (uint16_t)mjp; c.nb = (uint16_t)nb;
+  c.hh = (uint16_t)((h1 & 255) | ((h2 & 255) << 8));
+  c.geo = plain ? ((uint32_t)oi | ((uint32_t)oj << 12) | RF_GEO_OK) : 0u;
+  c.fp_lo = flo; c.fp_hi = fhi;
 }
 
 /* ------------------------------------------------------------------------------------ */
@@ -677,6 +704,14 @@ struct CombineStage {
   int32_t *mb_idx;            /* max_stack: beam slot of the m-th open member */
   int32_t *htab;              /* hcap: item index + 1, 0 = empty */
   int32_t hcap;               /* power of two >= 2 * chunk_cap */
+  /* what the enumeration needs of every open member, staged once per folding step so that decoding
+   * a combination touches global memory only for the stem records themselves */
+  uint64_t *m_lo, *m_hi;      /* max_stack: fingerprint of the member */
+  int32_t *m_e;               /* max_stack: its energy */
+  int32_t *m_pool;            /* max_stack: first pair of its regions in `pool`, -1: not staged (read from the arena) */
+  int32_t *m_nact;            /* max_stack: regions with candidates */
+  int32_t *pool;              /* 2 * pool_cap: (candidates, first stem record) of those regions, in node-list order */
+  int32_t pool_cap;
 };
 RF_HD size_t stage_carve(CombineStage &S, char *base, int chunk_cap, int max_stack) {
   size_t off = 0;
@@ -698,6 +733,13 @@ RF_HD size_t stage_carve(CombineStage &S, char *base, int chunk_cap, int max_sta
   RF_SCARVE(mem, int32_t, chunk_cap);
   RF_SCARVE(mb_idx, int32_t, max_stack);
   RF_SCARVE(htab, int32_t, hcap);
+  RF_SCARVE(m_lo, uint64_t, max_stack);
+  RF_SCARVE(m_hi, uint64_t, max_stack);
+  RF_SCARVE(m_e, int32_t, max_stack);
+  RF_SCARVE(m_pool, int32_t, max_stack);
+  RF_SCARVE(m_nact, int32_t, max_stack);
+  S.pool_cap = 3 * max_stack + 16;
+  RF_SCARVE(pool, int32_t, 2 * (size_t)S.pool_cap);
 #undef RF_SCARVE
   return align_up(off, 16);
 }
@@ -1111,18 +1153,11 @@ struct Fold {
         Cand &c = A.cand[off + at];
         const uint32_t ij = W.r_stem[r];
         const int mip = ij >> 16, mjp = ij & 0xffff, nb = W.r_nb[r];
-        c.dE = W.r_dE[r]; c.mip = (uint16_t)mip; c.mjp = (uint16_t)mjp; c.nb = (uint16_t)nb;
-        c.rank = (uint16_t)r; c.pad_ = 0;
+        c.dE = W.r_dE[r];
+        cand_geometry(c, W.pos, W.brcnt, mip, mjp, nb);
         CandKid &ck = A.ckid[off + at];
         ck.inner_id = (mjp - mip > 1) ? -1 : -2;                       /* rafft.py:130 */
         ck.outer_id = (mip - (nb - 1) > 0 || mjp + nb < lv) ? -1 : -2; /* rafft.py:141 */
-        uint64_t flo = 0, fhi = 0;
-        for (int k = 0; k < nb; k++) {
-          uint64_t l1, h1;
-          pair_fp(W.pos[mip - k], W.pos[mjp + k], l1, h1);
-          flo += l1; fhi += h1;
-        }
-        c.fp_lo = flo; c.fp_hi = fhi;
       RF_WPAR_END
     }
     RF_WSINGLE_BEGIN
@@ -1195,6 +1230,47 @@ struct Fold {
           }
         }
         at[j] = A.ncoff[S.nl_off + k] + (int)dgt;
+      }
+      int de[4];
+      uint64_t l[4], h[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        de[j] = 0; l[j] = 0; h[j] = 0;
+        if (at[j] >= 0) {
+          const Cand &cd = A.cand[at[j]];
+          de[j] = cd.dE; l[j] = cd.fp_lo; h[j] = cd.fp_hi;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; j++) { e += de[j]; lo += l[j]; hi += h[j]; }
+    }
+    if (lo == 0) lo = 1; /* 0 marks an empty slot of the seen table */
+  }
+
+  /* the same for the m-th open member, from the staged copy of its regions */
+  RF_FN void combo_eval_staged(int m, uint64_t combo, int &e, uint64_t &lo, uint64_t &hi) const {
+    const int po = cs.m_pool[m];
+    if (po < 0) { combo_eval(A.store[A.beam[cs.mb_idx[m]]], combo, e, lo, hi); return; }
+    e = cs.m_e[m]; lo = cs.m_lo[m]; hi = cs.m_hi[m];
+    const int32_t *pp = cs.pool + 2 * po;
+    for (int a0 = cs.m_nact[m] - 1; a0 >= 0; a0 -= 4) {
+      int at[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int a = a0 - j;
+        at[j] = -1;
+        if (a < 0) continue;
+        const uint32_t c = (uint32_t)pp[2 * a];
+        uint32_t dgt = 0;
+        if (c != 1) {
+          if ((combo >> 32) == 0) { /* the usual case: 32-bit division */
+            const uint32_t c32 = (uint32_t)combo, q = c32 / c;
+            dgt = c32 - q * c; combo = q;
+          } else {
+            dgt = (uint32_t)(combo % c); combo /= c;
+          }
+        }
+        at[j] = pp[2 * a + 1] + (int)dgt;
       }
       int de[4];
       uint64_t l[4], h[4];
@@ -1438,6 +1514,26 @@ struct Fold {
       cs.mb_pre[nm] = pre;
       sh->tmp0 = nm;
     RF_SINGLE_END
+    /* the open members' regions with candidates, staged (pool slots are handed out in any order;
+     * a member that does not fit keeps reading the arena) */
+    RF_SINGLE_BEGIN
+      sh->tmp1 = 0;
+    RF_SINGLE_END
+    RF_PAR_BEGIN(m, sh->tmp0)
+      const StoreRec &S = A.store[A.beam[cs.mb_idx[m]]];
+      const int na = (int)S.nact;
+      int po = Exec::atomic_add(&sh->tmp1, na);
+      if (po + na > cs.pool_cap) po = -1;
+      cs.m_pool[m] = po; cs.m_nact[m] = na;
+      cs.m_e[m] = S.e; cs.m_lo[m] = S.fp_lo; cs.m_hi[m] = S.fp_hi;
+      if (po >= 0) {
+        int a = 0;
+        for (int k = 0; k < S.nl_n; k++) {
+          const int c = A.ncnt[S.nl_off + k];
+          if (c > 0) { cs.pool[2 * (po + a)] = c; cs.pool[2 * (po + a) + 1] = A.ncoff[S.nl_off + k]; a++; }
+        }
+      }
+    RF_PAR_END
     /* P2b: the open members are enumerated one after the other while nb_branch < max_branch
      *      (rafft.py:180-203), a chunk of the flattened (member, combination) space at a time */
     const int CH = caps.chunk_cap;
@@ -1454,9 +1550,8 @@ struct Fold {
       RF_PAR_BEGIN(i, chunk)
         const uint64_t gi = g + (uint64_t)i;
         const int m = member_of(gi, nm);
-        const StoreRec &S = A.store[A.beam[cs.mb_idx[m]]];
         int e_; uint64_t lo_, hi_;
-        combo_eval(S, gi - cs.mb_pre[m], e_, lo_, hi_);
+        combo_eval_staged(m, gi - cs.mb_pre[m], e_, lo_, hi_);
         cs.e[i] = e_; cs.lo[i] = lo_; cs.hi[i] = hi_; cs.mem[i] = m;
         cs.flag[i] = !seen_has(lo_, hi_);
       RF_PAR_END
@@ -1723,13 +1818,17 @@ struct Fold {
       int side = A.todo[3 * a + 2];
       int mip = cd.mip, mjp = cd.mjp, nb = cd.nb;
       int ci, cj, lo1, hi1, xp, xq, lo2, hi2, clv;
+      const bool plain = (cd.geo & RF_GEO_OK) != 0; /* geometry in the stem record: no walk over the loop's segments */
+      const int oi = (int)(cd.geo & 0xfffu), oj = (int)((cd.geo >> 12) & 0xfffu), h1 = cd.hh & 255, h2 = cd.hh >> 8;
       if (side == 0) { /* get_inner_loop (utils.py:148-152): local (mip, mjp) exclusive */
-        ci = pos_of(par, mip); cj = pos_of(par, mjp); lo1 = seg_of(par, mip); hi1 = seg_of(par, mjp);
+        if (plain) { ci = oi; cj = oj; lo1 = h1; hi1 = h2; }
+        else { ci = pos_of(par, mip); cj = pos_of(par, mjp); lo1 = seg_of(par, mip); hi1 = seg_of(par, mjp); }
         xp = -1; xq = -1; lo2 = 0; hi2 = 0; clv = mjp - mip - 1;
       } else { /* get_outer_loop (utils.py:141-145): local [0, mip-nb] ++ [mjp+nb, lv) */
         int io = mip - nb + 1, jo = mjp + nb - 1;
-        ci = par.ci; cj = par.cj; lo1 = 0; hi1 = seg_of(par, io); xp = pos_of(par, io); xq = pos_of(par, jo);
-        lo2 = seg_of(par, jo); hi2 = par.br_n; clv = io + (par.lv - 1 - jo);
+        ci = par.ci; cj = par.cj; lo1 = 0; hi2 = par.br_n; clv = io + (par.lv - 1 - jo);
+        if (plain) { hi1 = h1; xp = oi - (nb - 1); xq = oj + (nb - 1); lo2 = h2; }
+        else { hi1 = seg_of(par, io); xp = pos_of(par, io); xq = pos_of(par, jo); lo2 = seg_of(par, jo); }
       }
       if (!build_node(node_base + a, ci, cj, &par, lo1, hi1, xp, xq, lo2, hi2, clv)) fail(ST_ERR_CAPACITY);
     RF_PAR_END
@@ -1807,7 +1906,10 @@ struct Fold {
           const CandKid &kid = A.ckid[nd.cand_off + dgt];
           if (kid.outer_id != -2) A.nlist[--w] = kid.outer_id;
           if (kid.inner_id != -2) A.nlist[--w] = kid.inner_id;
-          for (int q = 0; q < cd.nb; q++) {
+          if (cd.geo & RF_GEO_OK) {
+            const int oi = (int)(cd.geo & 0xfffu), oj = (int)((cd.geo >> 12) & 0xfffu);
+            for (int q = 0; q < cd.nb; q++) { db[oi - q] = '('; db[oj + q] = ')'; }
+          } else for (int q = 0; q < cd.nb; q++) {
             db[pos_of(nd, cd.mip - q)] = '(';
             db[pos_of(nd, cd.mjp + q)] = ')';
           }
