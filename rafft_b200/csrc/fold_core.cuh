@@ -704,14 +704,6 @@ struct CombineStage {
   int32_t *mb_idx;            /* max_stack: beam slot of the m-th open member */
   int32_t *htab;              /* hcap: item index + 1, 0 = empty */
   int32_t hcap;               /* power of two >= 2 * chunk_cap */
-  /* what the enumeration needs of every open member, staged once per folding step so that decoding
-   * a combination touches global memory only for the stem records themselves */
-  uint64_t *m_lo, *m_hi;      /* max_stack: fingerprint of the member */
-  int32_t *m_e;               /* max_stack: its energy */
-  int32_t *m_pool;            /* max_stack: first pair of its regions in `pool`, -1: not staged (read from the arena) */
-  int32_t *m_nact;            /* max_stack: regions with candidates */
-  int32_t *pool;              /* 2 * pool_cap: (candidates, first stem record) of those regions, in node-list order */
-  int32_t pool_cap;
 };
 RF_HD size_t stage_carve(CombineStage &S, char *base, int chunk_cap, int max_stack) {
   size_t off = 0;
@@ -733,13 +725,6 @@ RF_HD size_t stage_carve(CombineStage &S, char *base, int chunk_cap, int max_sta
   RF_SCARVE(mem, int32_t, chunk_cap);
   RF_SCARVE(mb_idx, int32_t, max_stack);
   RF_SCARVE(htab, int32_t, hcap);
-  RF_SCARVE(m_lo, uint64_t, max_stack);
-  RF_SCARVE(m_hi, uint64_t, max_stack);
-  RF_SCARVE(m_e, int32_t, max_stack);
-  RF_SCARVE(m_pool, int32_t, max_stack);
-  RF_SCARVE(m_nact, int32_t, max_stack);
-  S.pool_cap = 3 * max_stack + 16;
-  RF_SCARVE(pool, int32_t, 2 * (size_t)S.pool_cap);
 #undef RF_SCARVE
   return align_up(off, 16);
 }
@@ -1247,47 +1232,6 @@ struct Fold {
     if (lo == 0) lo = 1; /* 0 marks an empty slot of the seen table */
   }
 
-  /* the same for the m-th open member, from the staged copy of its regions */
-  RF_FN void combo_eval_staged(int m, uint64_t combo, int &e, uint64_t &lo, uint64_t &hi) const {
-    const int po = cs.m_pool[m];
-    if (po < 0) { combo_eval(A.store[A.beam[cs.mb_idx[m]]], combo, e, lo, hi); return; }
-    e = cs.m_e[m]; lo = cs.m_lo[m]; hi = cs.m_hi[m];
-    const int32_t *pp = cs.pool + 2 * po;
-    for (int a0 = cs.m_nact[m] - 1; a0 >= 0; a0 -= 4) {
-      int at[4];
-#pragma unroll
-      for (int j = 0; j < 4; j++) {
-        const int a = a0 - j;
-        at[j] = -1;
-        if (a < 0) continue;
-        const uint32_t c = (uint32_t)pp[2 * a];
-        uint32_t dgt = 0;
-        if (c != 1) {
-          if ((combo >> 32) == 0) { /* the usual case: 32-bit division */
-            const uint32_t c32 = (uint32_t)combo, q = c32 / c;
-            dgt = c32 - q * c; combo = q;
-          } else {
-            dgt = (uint32_t)(combo % c); combo /= c;
-          }
-        }
-        at[j] = pp[2 * a + 1] + (int)dgt;
-      }
-      int de[4];
-      uint64_t l[4], h[4];
-#pragma unroll
-      for (int j = 0; j < 4; j++) {
-        de[j] = 0; l[j] = 0; h[j] = 0;
-        if (at[j] >= 0) {
-          const Cand &cd = A.cand[at[j]];
-          de[j] = cd.dE; l[j] = cd.fp_lo; h[j] = cd.fp_hi;
-        }
-      }
-#pragma unroll
-      for (int j = 0; j < 4; j++) { e += de[j]; lo += l[j]; hi += h[j]; }
-    }
-    if (lo == 0) lo = 1; /* 0 marks an empty slot of the seen table */
-  }
-
   /* in-chunk duplicate detection: item i (fingerprint cs.lo/hi[i]) enters the table; items with
    * the same fingerprint share a slot, which ends up holding the smallest item index + 1 */
   RF_FN int chunk_insert(int i) {
@@ -1514,26 +1458,6 @@ struct Fold {
       cs.mb_pre[nm] = pre;
       sh->tmp0 = nm;
     RF_SINGLE_END
-    /* the open members' regions with candidates, staged (pool slots are handed out in any order;
-     * a member that does not fit keeps reading the arena) */
-    RF_SINGLE_BEGIN
-      sh->tmp1 = 0;
-    RF_SINGLE_END
-    RF_PAR_BEGIN(m, sh->tmp0)
-      const StoreRec &S = A.store[A.beam[cs.mb_idx[m]]];
-      const int na = (int)S.nact;
-      int po = Exec::atomic_add(&sh->tmp1, na);
-      if (po + na > cs.pool_cap) po = -1;
-      cs.m_pool[m] = po; cs.m_nact[m] = na;
-      cs.m_e[m] = S.e; cs.m_lo[m] = S.fp_lo; cs.m_hi[m] = S.fp_hi;
-      if (po >= 0) {
-        int a = 0;
-        for (int k = 0; k < S.nl_n; k++) {
-          const int c = A.ncnt[S.nl_off + k];
-          if (c > 0) { cs.pool[2 * (po + a)] = c; cs.pool[2 * (po + a) + 1] = A.ncoff[S.nl_off + k]; a++; }
-        }
-      }
-    RF_PAR_END
     /* P2b: the open members are enumerated one after the other while nb_branch < max_branch
      *      (rafft.py:180-203), a chunk of the flattened (member, combination) space at a time */
     const int CH = caps.chunk_cap;
@@ -1550,8 +1474,9 @@ struct Fold {
       RF_PAR_BEGIN(i, chunk)
         const uint64_t gi = g + (uint64_t)i;
         const int m = member_of(gi, nm);
+        const StoreRec &S = A.store[A.beam[cs.mb_idx[m]]];
         int e_; uint64_t lo_, hi_;
-        combo_eval_staged(m, gi - cs.mb_pre[m], e_, lo_, hi_);
+        combo_eval(S, gi - cs.mb_pre[m], e_, lo_, hi_);
         cs.e[i] = e_; cs.lo[i] = lo_; cs.hi[i] = hi_; cs.mem[i] = m;
         cs.flag[i] = !seen_has(lo_, hi_);
       RF_PAR_END
