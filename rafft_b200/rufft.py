@@ -60,7 +60,7 @@ class FastFoldingGraph:
     """Drop-in for `rafft.FastFoldingGraph` of the Rust twin (bindings.rs:11-81)."""
 
     def __init__(self, sequence, number_of_lags=100, number_of_branches=1000, saved_trajectories=1,
-                 au=2.0, gc=3.0, gu=1.0, min_unpaired=3, min_loop_energy=0.0, device=0):
+                 au=2.0, gc=3.0, gu=1.0, min_unpaired=3, min_loop_energy=0.0, device=0, parameters=None):
         for ch in sequence:
             if ch not in _VALID:
                 # EncodedSequence::with_basepair_weights -> Err(InvalidNucleotide), which
@@ -76,6 +76,8 @@ class FastFoldingGraph:
         self.min_unpaired = int(min_unpaired)
         self.min_loop_energy = float(min_loop_energy)
         self.device = int(device)
+        # a ViennaRNA parameter file (rufft --params, vienna.rs:75-81 vrna_params_load) replaces the built-in tables
+        self.parameters = parameters
         # RafftGraph::new holds only the root (folding_graph.rs:38-71)
         self._nodes = [(0, "." * len(sequence), 0)]  # (depth, dot-bracket, E in dcal/mol)
         self._edges = []
@@ -88,7 +90,12 @@ class FastFoldingGraph:
         full trajectory, then the folding graph of that trajectory."""
         if self._built:
             return
-        ctx = get_context(self.device)
+        if self.parameters is not None:
+            from .params import read_par
+            from .rafft import FoldContext
+            ctx = FoldContext(self.device, read_par(self.parameters))
+        else:
+            ctx = get_context(self.device)
         _, trajectory = fold_batch([self.sequence], self.number_of_lags, self.saved_trajectories,
                                    self.number_of_branches, self.min_unpaired, self.min_loop_energy,
                                    True, 37.0, self.gc, self.au, self.gu, context=ctx)[0]

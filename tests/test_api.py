@@ -136,3 +136,31 @@ def test_multi_device_ranges(native_lib_path):
     assert plan_ranges([500, 10, 10, 10], 4).tolist() == [0, 1, 2, 3, 4]
     assert plan_ranges([10, 10, 10, 500], 2).tolist() == [0, 3, 4]
     assert plan_ranges([], 2).tolist() == [0, 0, 0]
+
+
+def test_parameter_file_roundtrip(tmp_path, native_lib_path):
+    """ViennaRNA `## RNAfold parameter file v2.0` reader (the reference loads such files,
+    rafft-rs/src/vienna.rs:75-81): the built-in tables written out and read back are identical;
+    comments, INF and a changed entry survive; malformed files are refused"""
+    from rafft_b200 import _native as N
+    from rafft_b200 import params as P
+    ep = N.default_energy_params()
+    path = str(tmp_path / "t.par")
+    P.write_par(ep, path)
+    ep2 = P.read_par(path)
+    assert bytes(ep) == bytes(ep2)
+    txt = open(path).read()
+    assert "# int22" in txt and "INF" in txt and txt.startswith("## RNAfold parameter file v2.0")
+    # ViennaRNA's own files carry /* */ comments between and inside the rows
+    txt = txt.replace("# stack\n", "# stack\n/* a comment\n over two lines */\n").replace("  -240  -330", "  -250 /* CG CG */  -330", 1)
+    open(path, "w").write(txt)
+    ep3 = P.read_par(path)
+    assert ep3.stack[0] == -250 and ep3.stack[1] == -330 and list(ep3.int22) == list(ep.int22)
+    assert ep3.hairpin[0] == P.INF and ep3.terminal_au == ep.terminal_au and ep3.lxc == ep.lxc
+    assert [ep3.tetra[k].value for k in range(ep3.n_tetra)] == [ep.tetra[k].value for k in range(ep.n_tetra)]
+    open(path, "w").write(txt.replace("# int21", "# int21_renamed"))
+    with pytest.raises(ValueError):
+        P.read_par(path)
+    open(path, "w").write("not a parameter file\n")
+    with pytest.raises(ValueError):
+        P.read_par(path)

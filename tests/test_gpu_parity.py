@@ -370,3 +370,26 @@ print("ok")
     env = dict(os.environ, RAFFT_SEEN_GEN0="65533")
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env)
     assert out.returncode == 0 and out.stdout.strip() == "ok", out.stderr[-2000:]
+
+
+def test_parameter_file_context(ctx, tmp_path):
+    "a context built from a ViennaRNA parameter file: the built-in tables written out fold identically; a changed stack entry changes energies"
+    from rafft_b200 import _native as N
+    from rafft_b200 import params as P
+    from rafft_b200 import rafft as R
+    path = str(tmp_path / "t.par")
+    ep = N.default_energy_params()
+    P.write_par(ep, path)
+    seqs = config_batch("cfg2", 30)
+    want, _ = gpu_steps(ctx, seqs, nb_mode=100, max_stack=10)
+    c2 = R.FoldContext(0, P.read_par(path))
+    got, _ = gpu_steps(c2, seqs, nb_mode=100, max_stack=10)
+    assert got == want
+    c2.close()
+    ep.stack[1] -= 100                      # CG followed by GC, 1 kcal/mol more stable
+    ep.stack[6] -= 100                      # and its mirror entry
+    P.write_par(ep, path)
+    c3 = R.FoldContext(0, P.read_par(path))
+    other, _ = gpu_steps(c3, seqs, nb_mode=100, max_stack=10)
+    assert other != want
+    c3.close()
