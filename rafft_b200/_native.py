@@ -74,7 +74,7 @@ class Result(C.Structure):
 FAMILY_NAMES = ("gather", "expand_fast", "expand_generic", "combine", "select", "materialise", "advance", "other")
 # kernel names (as ncu prints them) of every family
 FAMILY_KERNELS = {"gather": ("k_gather",), "expand_fast": ("k_expand_fast", "k_expand_big"), "expand_generic": ("k_expand",),
-                  "combine": ("k_combine",), "select": ("k_select",), "materialise": ("k_materialise",),
+                  "combine": ("k_combine",), "select": ("k_select",), "materialise": ("k_materialise", "k_beam"),
                   "advance": ("k_advance",), "other": ("k_init", "k_finish", "k_ctl_reset")}
 
 

@@ -7,6 +7,7 @@
 #include <math.h>
 #include <stdint.h>
 #include <string.h>
+#include <stdlib.h>
 #include <string>
 #include "../../include/rafft_b200.h"
 #include "fold_core.cuh"
@@ -147,6 +148,10 @@ inline Caps make_caps(int L_max, const FoldParams &F, int nthreads, int scale) {
   int64_t mbc = mb < 4096LL * scale ? mb : 4096LL * scale; /* children kept per step */
   c.L_max = L_max < 16 ? 16 : L_max;
   c.chunk_cap = (int32_t)(4 * nthreads > ms ? 4 * nthreads : ms);
+  if (const char *e = getenv("RAFFT_CHUNK")) { /* tuning: stem combinations examined per block phase */
+    const int v = atoi(e);
+    if (v >= 64 && v <= 8192 && v >= ms) c.chunk_cap = v;
+  }
   int64_t kmin = 2 * (int64_t)c.L_max > F.nb_mode ? 2 * (int64_t)c.L_max : F.nb_mode;
   c.key_cap = pow2_at_least(kmin < 32 ? 32 : kmin);
   c.mask_words = c.L_max / 32 + 2;

@@ -81,6 +81,7 @@ struct WaveCtx {
   int32_t *alist;     /* two lists of acap wave slots: the sequences still folding */
   int32_t acap;
   int32_t sel_smem;   /* bytes of shared memory for the energies under selection (0: global) */
+  int32_t fuse;       /* 1: select + materialise + the next step's gather run as one kernel (k_beam) */
   int32_t *h_prog;    /* host-mapped: [0] iterations finished, [1] 1 once no sequence is active */
   OutBuf out;
 };
@@ -148,6 +149,12 @@ __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_init(RF_WAVE_PARAM) {
   const int64_t o = c.offs[si];
   if (threadIdx.x == 0) { sh.seq_off = o; c.alist[j] = j; }
   f.phase_init(c.seqs + o, (int)(c.offs[si + 1] - o), si);
+  if (c.fuse) { /* the first folding step's gather: the root region goes on a work list */
+    f.Q = c.Q;
+    f.Q.self = j;
+    __syncthreads();
+    f.phase_gather();
+  }
   BlockBind::store(c, &sh, j);
 }
 
@@ -161,9 +168,21 @@ __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_gather(RF_WAVE_PARAM) 
   RF_END_ACTIVE
 }
 
+/* the expansion work lists of this step are consumed once the expansion kernels have ended; with
+ * the fused chain the NEXT step's gather fills them again inside k_beam, so they are cleared here */
+__device__ __forceinline__ void clear_work_lists(LoopCtl *ctl) {
+  const int t = threadIdx.x;
+  if (t < RF_FAST_LISTS) { ctl->fast_total[t] += ctl->n_fast[t]; ctl->n_fast[t] = 0; ctl->fast_next[t] = 0; }
+  if (t == 0) {
+    ctl->generic_total += ctl->n_tasks; ctl->n_tasks = 0;
+    ctl->big_total += ctl->n_big; ctl->n_big = 0; ctl->big_next = 0;
+  }
+}
+
 __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_combine(RF_WAVE_PARAM) {
   __shared__ SeqState sh;
   extern __shared__ __align__(16) char combine_smem[];
+  if (c.fuse && blockIdx.x == 0) clear_work_lists(c.ctl);
   RF_FOR_ACTIVE(1)
     Fold f(c.E, c.prm, c.caps);
     if (!BlockBind::load(c, f, &sh, j, true)) continue;
@@ -197,18 +216,36 @@ __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_materialise(RF_WAVE_PA
   RF_END_ACTIVE
 }
 
+/* select + materialise of this folding step and the gather of the next one, per sequence: two
+ * launches and two round trips of the sequence state less per step than the separate kernels */
+__global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_beam(RF_WAVE_PARAM) {
+  __shared__ SeqState sh;
+  extern __shared__ __align__(16) char select_smem[];
+  int32_t *next_list = c.alist + (size_t)(c.ctl->parity ^ 1) * (size_t)c.acap;
+  RF_FOR_ACTIVE(2)
+    Fold f(c.E, c.prm, c.caps);
+    if (!BlockBind::load(c, f, &sh, j, true)) continue;
+    if (c.sel_smem) f.A.sel_e = (int32_t *)select_smem;
+    f.phase_select();
+    __syncthreads();
+    f.phase_materialise();
+    __syncthreads();
+    f.phase_gather();
+    if (threadIdx.x == 0 && sh.active) next_list[atomicAdd(&c.ctl->n_next, 1)] = j;
+    BlockBind::store(c, &sh, j);
+  RF_END_ACTIVE
+}
+
 /* end of a folding iteration: the next active list becomes the current one, the work lists and
  * cursors are cleared, and the loop condition is set (graph WHILE node) / published to the host
  * (stream mode) */
-__global__ void k_advance(LoopCtl *ctl, int32_t *h_prog, cudaGraphConditionalHandle handle, int use_handle) {
+__global__ void k_advance(LoopCtl *ctl, int32_t *h_prog, cudaGraphConditionalHandle handle, int use_handle, int fuse) {
   const int t = threadIdx.x;
-  if (t < RF_FAST_LISTS) { ctl->fast_total[t] += ctl->n_fast[t]; ctl->n_fast[t] = 0; ctl->fast_next[t] = 0; }
+  if (!fuse) clear_work_lists(ctl);
   if (t < 4) ctl->work[t] = 0;
   if (t == 0) {
-    ctl->generic_total += ctl->n_tasks;
-    ctl->big_total += ctl->n_big; ctl->n_big = 0; ctl->big_next = 0;
     const int n = ctl->n_next;
-    ctl->n_cur = n; ctl->n_next = 0; ctl->parity ^= 1; ctl->n_tasks = 0;
+    ctl->n_cur = n; ctl->n_next = 0; ctl->parity ^= 1;
     const int it = ++ctl->iters;
     if (use_handle) cudaGraphSetConditional(handle, n > 0 ? 1u : 0u);
     if (n == 0) h_prog[1] = 1;
@@ -589,6 +626,8 @@ struct rafft_ctx {
   int lanes = 0;            /* 0 automatic, 1..RF_MAX_LANES forced */
   int profile = 0;          /* per-kernel-family CUDA events (stepwise loop, one lane) */
   int persist = 1;          /* blocks per SM of the persistent block-scope kernels = occupancy * persist */
+  int fuse = 0;             /* 1: select + materialise + next gather as one kernel, k_beam (RAFFT_FUSE=1; measured: -2 % at 1,250
+                               sequences, +2 % at 10,000: profiles/r02_fuse.md) */
   int lane_split = 50;      /* per cent of the estimated cost that goes to lane 0 when a call runs two lanes */
   int64_t mem_budget = 0;   /* bytes this context may use for arenas + scratch */
   double traj_ratio = 5.0;  /* structures per (sequence x max_stack) of the last traj = 1 call */
@@ -782,6 +821,8 @@ int rafft_create(rafft_ctx **out, int cuda_device, const rafft_energy_params *ep
     if (s) { int v = atoi(s); if (v >= 0 && v <= RF_MAX_LANES) ctx->lanes = v; }
     s = getenv("RAFFT_PROFILE");
     if (s) ctx->profile = atoi(s) != 0;
+    s = getenv("RAFFT_FUSE");
+    if (s) ctx->fuse = atoi(s) != 0;
     s = getenv("RAFFT_LANE_SPLIT");
     if (s) { int v = atoi(s); if (v >= 5 && v <= 95) ctx->lane_split = v; }
     s = getenv("RAFFT_PERSIST");
@@ -807,6 +848,7 @@ int rafft_set_option(rafft_ctx *ctx, const char *name, int64_t value) {
   else if (k == "max_wave" && value >= 0) ctx->max_wave = value;
   else if (k == "persist" && value >= 1 && value <= 8) ctx->persist = (int)value;
   else if (k == "lane_split" && value >= 5 && value <= 95) ctx->lane_split = (int)value;
+  else if (k == "fuse" && (value == 0 || value == 1)) ctx->fuse = (int)value;
   else { ctx->err = "rafft_set_option: unknown option or value out of range: " + k; return RAFFT_ERR_ARG; }
   return RAFFT_OK;
 }
@@ -945,7 +987,7 @@ static void emit_iteration(Emit &E, WavePlan &P, cudaGraphConditionalHandle hand
   int ne = 0;
   auto mark = [&]() { if (fam_ev && E.err == cudaSuccess) E.err = cudaEventRecord(fam_ev[ne++], E.stream); };
   mark();
-  E.kernel((const void *)k_gather, dim3(P.g_gather), dim3(P.T_gather), 0, a_wc);
+  if (!wc.fuse) E.kernel((const void *)k_gather, dim3(P.g_gather), dim3(P.T_gather), 0, a_wc);
   mark();
   if (P.use_fast) E.kernel((const void *)P.fsh->fn, dim3(P.g_fast), dim3(P.fsh->threads), P.fast_smem, a_wc);
   if (P.use_big) E.kernel((const void *)k_expand_big, dim3(P.g_big), dim3(RF_BIG_THREADS), P.big_smem, a_wc);
@@ -960,13 +1002,15 @@ static void emit_iteration(Emit &E, WavePlan &P, cudaGraphConditionalHandle hand
   mark();
   E.kernel((const void *)k_combine, dim3(P.g_combine), dim3(P.T_combine), P.stage_bytes, a_wc);
   mark();
-  E.kernel((const void *)k_select, dim3(P.g_select), dim3(P.T_select), (size_t)wc.sel_smem, a_wc);
+  if (!wc.fuse) E.kernel((const void *)k_select, dim3(P.g_select), dim3(P.T_select), (size_t)wc.sel_smem, a_wc);
   mark();
-  E.kernel((const void *)k_materialise, dim3(P.g_mat), dim3(P.T_mat), 0, a_wc);
+  if (wc.fuse) E.kernel((const void *)k_beam, dim3(P.g_mat), dim3(P.T_mat), (size_t)wc.sel_smem, a_wc);
+  else E.kernel((const void *)k_materialise, dim3(P.g_mat), dim3(P.T_mat), 0, a_wc);
   mark();
   LoopCtl *ctl = wc.ctl;
   int32_t *hp = wc.h_prog;
-  void *a_adv[] = {&ctl, &hp, &handle, &use_handle};
+  int fuse = wc.fuse;
+  void *a_adv[] = {&ctl, &hp, &handle, &use_handle, &fuse};
   E.kernel((const void *)k_advance, dim3(1), dim3(32), 0, a_adv);
   mark();
 }
@@ -1182,6 +1226,7 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
     wc.ctl = ctl;
     wc.alist = (int32_t *)ln.alist.p; wc.acap = (int32_t)wave;
     wc.h_prog = h_prog;
+    wc.fuse = ctx->fuse;
     wc.Q.n_tasks = &ctl->n_tasks; wc.Q.cap = (int32_t)qcap; wc.Q.task = (int32_t *)ln.tasks.p;
     wc.Q.scratch = (char *)ln.scratch.p; wc.Q.self = 0;
     wc.Q.n_fast = ctl->n_fast; wc.Q.fast_cap = (int32_t)fcap; wc.Q.fast_task = (int32_t *)ln.ftasks.p;
@@ -1244,7 +1289,7 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
       P.g_gather = grid_of((const void *)k_gather, P.T_gather, 0);
       P.g_combine = grid_of((const void *)k_combine, P.T_combine, P.stage_bytes);
       P.g_select = grid_of((const void *)k_select, P.T_select, (size_t)wc.sel_smem);
-      P.g_mat = grid_of((const void *)k_materialise, P.T_mat, 0);
+      P.g_mat = wc.fuse ? grid_of((const void *)k_beam, P.T_mat, (size_t)wc.sel_smem) : grid_of((const void *)k_materialise, P.T_mat, 0);
       /* every fold of an arena tags its `seen` entries with a new generation; when the 16-bit
        * counter wraps the tables are zeroed once */
       if (++ln.seen_gen > 65535u) {
@@ -1255,7 +1300,7 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
       h_prog[0] = 0; h_prog[1] = 0; /* the lane's stream is idle here: no kernel writes them now */
       k_ctl_reset<<<1, 64, 0, ln.stream>>>(ctl, nw, (int)ln.seen_gen);
       T.launches++;
-      const int per_iter = 1 + (P.use_fast ? 1 : 0) + (P.use_big ? 1 : 0) + (P.any_generic ? 5 : 0) + 3 + 1;
+      const int per_iter = (P.use_fast ? 1 : 0) + (P.use_big ? 1 : 0) + (P.any_generic ? 5 : 0) + (wc.fuse ? 2 : 4) + 1;
       bool done = false;
       if (!profile && ctx->loop_mode == 0) {
         std::string why;
@@ -1289,7 +1334,8 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
             const int fams[7] = {FAM_GATHER, FAM_EXPAND_FAST, FAM_EXPAND_GENERIC, FAM_COMBINE, FAM_SELECT, FAM_MATERIALISE, FAM_ADVANCE};
             for (int f = 0; f < 7; f++) {
               LCK(cudaEventElapsedTime(&ms, ln.pev[f], ln.pev[f + 1]));
-              const bool ran = !(fams[f] == FAM_EXPAND_FAST && !P.use_fast) && !(fams[f] == FAM_EXPAND_GENERIC && !P.any_generic);
+              const bool ran = !(fams[f] == FAM_EXPAND_FAST && !P.use_fast) && !(fams[f] == FAM_EXPAND_GENERIC && !P.any_generic) &&
+                               !(wc.fuse && (fams[f] == FAM_GATHER || fams[f] == FAM_SELECT));
               if (ran) { T.fam_ms[fams[f]] += ms; T.fam_n[fams[f]] += fams[f] == FAM_EXPAND_GENERIC ? 5 : 1; }
               if (dbg) {
                 static const char *const nm[7] = {"gather", "fast", "generic", "combine", "select", "materialise", "advance"};

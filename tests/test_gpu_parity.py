@@ -128,7 +128,8 @@ def test_cfg3_full_batch_final_beams_vs_oracle(ctx, oracle):
 
 def test_lanes_and_loop_modes_give_identical_results(ctx):
     """one lane / two lanes (two priority streams, result copy of the first overlapping the fold of the
-    second), graph WHILE loop / stream loop with look-ahead / stepwise profile mode: same bytes"""
+    second), graph WHILE loop / stream loop with look-ahead / stepwise profile mode, fused beam kernel /
+    separate select, materialise and gather kernels: same bytes"""
     from rafft_b200 import rafft as R
     seqs = config_batch("cfg2", 1500)
     offs = np.zeros(len(seqs) + 1, dtype=np.int64)
@@ -136,8 +137,10 @@ def test_lanes_and_loop_modes_give_identical_results(ctx):
     sb, prm = "".join(seqs).encode(), R.make_params(100, 50, 1000, traj=True)
     ref = None
     try:
-        for lanes, loop, prof in ((1, 0, 0), (2, 0, 0), (2, 1, 0), (1, 1, 0), (1, 0, 1), (2, 0, 0)):
+        for lanes, loop, prof, fuse in ((1, 0, 0, 1), (2, 0, 0, 1), (2, 1, 0, 0), (1, 1, 0, 1), (1, 0, 1, 1), (1, 0, 1, 0),
+                                        (1, 0, 0, 0), (2, 0, 0, 1)):
             ctx.set_option("lanes", lanes); ctx.set_option("loop", loop); ctx.set_option("profile", prof)
+            ctx.set_option("fuse", fuse)
             raw = ctx.fold_raw(sb, offs, prm)
             assert raw.lanes == lanes and raw.loop_mode == (2 if prof else loop)
             cur = [np.array(a) for a in (raw.status, raw.struct_off, raw.energy, raw.db_off, raw.db, raw.step_off,
@@ -147,10 +150,10 @@ def test_lanes_and_loop_modes_give_identical_results(ctx):
             if ref is None:
                 ref = cur
             else:
-                assert all((a == b).all() for a, b in zip(ref, cur)), (lanes, loop, prof)
+                assert all((a == b).all() for a, b in zip(ref, cur)), (lanes, loop, prof, fuse)
             raw.close()
     finally:
-        ctx.set_option("lanes", 0); ctx.set_option("loop", 0); ctx.set_option("profile", 0)
+        ctx.set_option("lanes", 0); ctx.set_option("loop", 0); ctx.set_option("profile", 0); ctx.set_option("fuse", 0)
 
 
 def test_multi_device_entry_matches_single(ctx, oracle):
