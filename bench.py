@@ -236,6 +236,8 @@ def run_b200(args, wl):
             raise SystemExit("launch N > 1 with torchrun (one rank per GPU)")
     dist = None
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"  # the version banner goes to stdout, which carries the JSON line
         import torch.distributed as dist
         torch.cuda.set_device(local)
         dist.init_process_group("cpu:gloo,cuda:nccl", device_id=torch.device("cuda", local))
@@ -244,9 +246,9 @@ def run_b200(args, wl):
     ctx = R.FoldContext(local)   # fails loudly without the CUDA library / a GPU
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
-    def barrier():
+    def barrier(collective=True):
         torch.cuda.synchronize()
-        if dist is not None:
+        if dist is not None and collective:
             dist.barrier()
         torch.cuda.synchronize()
 
@@ -295,8 +297,10 @@ def run_b200(args, wl):
         raw.close()
         return len(sample), ok
 
-    def measure(sh, w, steps, warmup, want_e2e=True):
-        """device-resident and end-to-end legs of one shard; returns per-rank numbers (callers reduce)"""
+    def measure(sh, w, steps, warmup, want_e2e=True, collective=True):
+        """device-resident and end-to-end legs of one shard; returns per-rank numbers (callers reduce).
+        collective=False: only this rank runs it (no barrier across ranks)"""
+        sync = lambda: barrier(collective)  # noqa: E731
         prm = params_of(w)
         raw = None
         for _ in range(warmup):
@@ -307,7 +311,7 @@ def run_b200(args, wl):
         counters = raw.counters.copy()  # views die with the result
         lanes, loop_mode = raw.lanes, raw.loop_mode
         raw.close()
-        barrier()
+        sync()
         wall0 = time.perf_counter()
         kernel_ms, launches, iters = 0.0, 0, 0
         dev_steps = []
@@ -318,21 +322,21 @@ def run_b200(args, wl):
             launches += raw.kernel_launches
             iters = max(iters, raw.iterations)
             raw.close()
-        barrier()
+        sync()
         wall_dev = time.perf_counter() - wall0
         out = dict(kernel_ms=kernel_ms, launches=launches, iterations=iters, wall_dev=wall_dev, counters=counters,
                    lanes=lanes, loop_mode=loop_mode, dev_steps=dev_steps, e2e_s=0.0, e2e_steps=[], h2d=0, d2h=0)
         if want_e2e:
             for _ in range(min(warmup, 2)):
                 step_host(sh, prm)[1].close()
-            barrier()
+            sync()
             for _ in range(steps):
                 dt, raw = step_host(sh, prm)
                 out["e2e_s"] += dt
                 out["e2e_steps"].append(dt * 1e3)
                 out["h2d"], out["d2h"] = raw.h2d_bytes, raw.d2h_bytes
                 raw.close()
-            barrier()
+            sync()
         return out
 
     per_gpu = args.count or wl["count"]
@@ -449,7 +453,7 @@ def run_b200(args, wl):
             one_ms = 0.0
             if rank == 0:
                 whole = Shard(batch, dev, torch, np)
-                r1 = measure(whole, w, steps, 3, want_e2e=False)
+                r1 = measure(whole, w, steps, 3, want_e2e=False, collective=False)
                 one_ms = r1["kernel_ms"] / steps
                 del whole
             barrier()
