@@ -18,6 +18,13 @@ How the graph is read off the trajectory (all of it on the device except the num
           i is a pair of j, i != j): the connectivity of the reference's own kinetics
           (rafft/rafft_kin.py:48-56), computed by `rafft_kin_graph`; each edge once, as
           DiGraph::update_edge keeps them (folding_graph.rs:116).
+          DIVERGENCE from rafft-rs for `saved_trajectories` > 1: the Rust twin adds one edge
+          parent -> child per child it inserts (folding_graph.rs insert -> update_edge(parent,
+          node)); the nested-pair-set rule used here (the Python reference's kinetics rule) also
+          links an older beam member A, retained beside its child B, to B's child C (A's pairs are
+          a subset of C's), so `transition_rates()`, `directed_edges()` and `rufft -o` can carry
+          extra transitive edges there.  With `saved_trajectories` = 1 (the default and the only
+          setting the twin's own test pins) a step has one structure and the two rules coincide.
 """
 import math
 
