@@ -166,6 +166,28 @@ int rafft_fold_batch_device(rafft_ctx *ctx, const void *d_seqs, const void *d_of
 int rafft_eval_structures(rafft_ctx *ctx, const char *seqs, const char *structs,
                           const int64_t *offs, int32_t n, int32_t *energy_dcal);
 
+/* rafft_eval_structures for callers that cannot allocate (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same energies as rafft_eval_structures, with everything in device
+ * memory the CALLER owns -- d_seqs / d_structs: the concatenated letters and dot-brackets, d_offs:
+ * n + 1 int64 offsets (d_offs[0] = 0, d_offs[n] = total_len), d_energy_dcal: n int32 -- and the
+ * kernel's scratch (pair tables, base codes: 9 bytes per letter) in a file-scope device array of
+ * fixed size instead of a cudaMalloc'ed buffer.  The call makes no cudaMalloc / cudaFree /
+ * cudaHostAlloc and no allocating library call; it launches one kernel on the context's stream and
+ * returns after that stream has been synchronised (inputs must be complete before the call).
+ *   limit     total_len <= RAFFT_STATIC_EVAL_MAX_LETTERS (1,048,576 letters per call); more is
+ *             refused with RAFFT_ERR_ARG and a message naming the limit.  Per structure <= 4096 letters;
+ *             a structure whose offsets are out of range, longer than that, malformed or holding a
+ *             non-canonical pair gets INT32_MIN (as in rafft_eval_structures) and touches nothing.
+ *   cost      every GPU on which this library is loaded holds the array (9 MiB) until the process exits.
+ *   sharing   all calls on one device share the array, which keeps the last call's contents (the
+ *             kernel writes every element before it reads it; nothing must start at zero).  Calls that
+ *             overlap on the GPU -- two contexts of one device used from two threads -- RACE on it:
+ *             serialise them. */
+#define RAFFT_STATIC_EVAL_MAX_LETTERS 1048576
+int rafft_eval_structures_static(rafft_ctx *ctx, const void *d_seqs, const void *d_structs, const void *d_offs,
+                                 int32_t n, int64_t total_len, void *d_energy_dcal);
+
 /* Folding graph of the kinetics (reference rafft/rafft_kin.py:48-56 get_connected_prev, :106-115
  * the non-redundant numbering in kinetics).  db: n = step_off[n_steps] dot-bracket rows of L
  * characters, the folding steps concatenated (the blocks of a `rafft --traj` output).

@@ -19,7 +19,9 @@ CNT_N = len(COUNTER_NAMES)
 EXPORTS = ("rafft_version", "rafft_default_energy_params", "rafft_create", "rafft_destroy",
            "rafft_last_error", "rafft_fold_batch", "rafft_fold_batch_device", "rafft_result_free",
            "rafft_eval_structures", "rafft_kin_graph", "rafft_bp_distance_matrix",
-           "rafft_fold_batch_multi", "rafft_set_option", "rafft_int_peak", "rafft_plan_ranges", "rafft_device_count")
+           "rafft_fold_batch_multi", "rafft_set_option", "rafft_int_peak", "rafft_plan_ranges", "rafft_device_count",
+           "rafft_eval_structures_static")
+STATIC_EVAL_MAX_LETTERS = 1 << 20  # RAFFT_STATIC_EVAL_MAX_LETTERS
 
 
 class EnergyParams(C.Structure):
@@ -127,6 +129,9 @@ def lib():
     L.rafft_eval_structures.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_int64),
                                         C.c_int32, C.POINTER(C.c_int32)]
     L.rafft_eval_structures.restype = C.c_int
+    L.rafft_eval_structures_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64,
+                                               C.c_void_p]
+    L.rafft_eval_structures_static.restype = C.c_int
     L.rafft_kin_graph.argtypes = [C.c_void_p, C.c_char_p, C.c_int32, C.POINTER(C.c_int64), C.c_int32,
                                   C.POINTER(C.c_int32), C.POINTER(C.c_uint8), C.c_int64, C.POINTER(C.c_int64)]
     L.rafft_kin_graph.restype = C.c_int

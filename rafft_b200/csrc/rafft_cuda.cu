@@ -556,6 +556,98 @@ __global__ void eval_kernel(const DevEnergy *__restrict__ E, const char *__restr
   if (lane == 0) energy[warp] = nc ? INT32_MIN : (e > 2000000000LL ? 2000000000 : (int32_t)e);
 }
 
+/* ---- rafft_eval_structures_static: the evaluator without any allocation ------------------------
+ * Scratch of eval_kernel (pair table + stack: 2 ints per letter, base codes: 1 byte per letter) in a
+ * file-scope array of a fixed maximum size instead of a cudaMalloc'ed buffer.  Every GPU that loads
+ * this library holds the array (9 MiB) until the process exits.  All calls on one device share it
+ * and it keeps the contents of the last call; the kernel writes every element before reading it
+ * (pt[k] = -1 as lane 0 walks the structure, st[] pushed before popped, code[] filled first), so
+ * nothing has to start at zero -- but two calls that overlap on the GPU race on it.
+ * In host code the NAME of the array is a host-side stand-in, not a device address: the kernel gets
+ * the address that cudaGetSymbolAddress returned with the context's device current (static_scratch). */
+#define RF_STATIC_EVAL_MAX_LETTERS (1 << 20)
+static_assert(RF_STATIC_EVAL_MAX_LETTERS == RAFFT_STATIC_EVAL_MAX_LETTERS, "header and library disagree");
+static __device__ __align__(256) unsigned char g_static_eval_scratch[(size_t)RF_STATIC_EVAL_MAX_LETTERS * 9 + 256];
+
+/* eval_kernel with its scratch inside `scratch_base` (pt/st at byte 0, codes at 8 * max letters) and
+ * every offset checked on the device: a sequence whose letters do not lie inside [0, total_len], or
+ * is longer than 4096, gets INT32_MIN and touches nothing. */
+__global__ void eval_static_kernel(const DevEnergy *__restrict__ E, const char *__restrict__ seqs,
+                                   const char *__restrict__ dbs, const int64_t *__restrict__ offs, int n,
+                                   int64_t total_len, unsigned char *__restrict__ scratch_base,
+                                   int32_t *__restrict__ energy) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= n) return;
+  const int64_t o = offs[warp], o1 = offs[warp + 1];
+  if (o < 0 || o1 < o || o1 > total_len || o1 > (int64_t)RF_STATIC_EVAL_MAX_LETTERS || o1 - o > 4096) {
+    if (lane == 0) energy[warp] = INT32_MIN;
+    return;
+  }
+  const int L = (int)(o1 - o);
+  const char *seq = seqs + o, *db = dbs + o;
+  int32_t *pt = (int32_t *)scratch_base + 2 * o, *st = pt + L;
+  uint8_t *code = scratch_base + (size_t)8 * RF_STATIC_EVAL_MAX_LETTERS + o;
+  int bad = 0;
+  for (int k = lane; k < L; k += 32) {
+    char ch = seq[k];
+    int c = ch == 'A' ? 0 : ch == 'C' ? 1 : ch == 'G' ? 2 : ch == 'U' ? 3 : -1;
+    if (c < 0) { bad = 1; c = 0; }
+    code[k] = (uint8_t)c;
+  }
+  bad = __any_sync(0xffffffffu, bad);
+  __syncwarp();
+  int ok = 1;
+  if (lane == 0) {
+    int sp = 0;
+    for (int k = 0; k < L && ok; k++) {
+      pt[k] = -1;
+      if (db[k] == '(') st[sp++] = k;
+      else if (db[k] == ')') {
+        if (!sp) ok = 0;
+        else { int i = st[--sp]; pt[i] = k; pt[k] = i; }
+      } else if (db[k] != '.') ok = 0;
+    }
+    if (sp) ok = 0;
+  }
+  ok = __shfl_sync(0xffffffffu, ok, 0);
+  __syncwarp();
+  if (!ok || bad) { if (lane == 0) energy[warp] = INT32_MIN; return; }
+  EnergyView ev; ev.P = E; ev.s = code; ev.L = L;
+  long long e = 0;
+  int nc = 0;
+  for (int i = lane - 1; i < L; i += 32) { /* i = -1: exterior loop */
+    int j;
+    if (i >= 0) { j = pt[i]; if (j <= i) continue; if (pair_type(code[i], code[j]) < 0) { nc = 1; continue; } }
+    else j = L;
+    int nbr = 0, p1 = -1, q1 = -1, unp = 0;
+    for (int p = i + 1; p < j;) {
+      if (pt[p] > p) { if (!nbr) { p1 = p; q1 = pt[p]; } nbr++; p = pt[p] + 1; }
+      else { unp++; p++; }
+    }
+    if (i < 0) {
+      for (int p = 0; p < L;) {
+        if (pt[p] > p) { if (pair_type(code[p], code[pt[p]]) >= 0) e += e_extstem(ev, p, pt[p]); p = pt[p] + 1; }
+        else p++;
+      }
+    } else if (nbr == 0) e += e_hairpin(ev, i, j);
+    else if (nbr == 1) { if (pair_type(code[p1], code[q1]) >= 0) e += e_interior(ev, i, j, p1, q1); }
+    else {
+      int tt = pair_type(code[j], code[i]);
+      e += E->ml_closing + (long long)E->ml_base * unp + E->ml_intern +
+           E->mmM[tt * 16 + code[j - 1] * 4 + code[i + 1]] + (tt > 1 ? E->terminal_au : 0);
+      for (int p = i + 1; p < j;) {
+        if (pt[p] > p) { if (pair_type(code[p], code[pt[p]]) >= 0) e += e_mlstem(ev, p, pt[p]); p = pt[p] + 1; }
+        else p++;
+      }
+    }
+  }
+  for (int d = 16; d; d >>= 1) {
+    e += __shfl_xor_sync(0xffffffffu, e, d);
+    nc |= __shfl_xor_sync(0xffffffffu, nc, d);
+  }
+  if (lane == 0) energy[warp] = nc ? INT32_MIN : (e > 2000000000LL ? 2000000000 : (int32_t)e);
+}
+
 /* ------------------------------------------------------------------------------------ */
 /* host side                                                                             */
 
@@ -632,6 +724,7 @@ struct rafft_ctx {
   int64_t mem_budget = 0;   /* bytes this context may use for arenas + scratch */
   double traj_ratio = 5.0;  /* structures per (sequence x max_stack) of the last traj = 1 call */
   uint32_t gen0 = 0;
+  unsigned char *static_scratch = nullptr; /* device address of g_static_eval_scratch on this context's device */
   std::string err;
 };
 
@@ -1849,6 +1942,46 @@ int rafft_eval_structures(rafft_ctx *ctx, const char *seqs, const char *structs,
                                                                (uint8_t *)(d + o_code), (int32_t *)(d + o_e));
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(energy_dcal, d + o_e, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return RAFFT_OK;
+}
+
+/* The device address of the static scratch array on ctx's device: looked up once per context (a
+ * context is bound to one device), with that device current.  No allocation. */
+static int static_scratch_of(rafft_ctx *ctx, unsigned char **out) {
+  if (!ctx->static_scratch) {
+    CK(cudaSetDevice(ctx->device));
+    void *p = nullptr;
+    CK(cudaGetSymbolAddress(&p, g_static_eval_scratch));
+    if (!p) { ctx->err = "rafft_eval_structures_static: no device address for the static scratch"; return RAFFT_ERR_CUDA; }
+    ctx->static_scratch = (unsigned char *)p;
+  }
+  *out = ctx->static_scratch;
+  return RAFFT_OK;
+}
+
+int rafft_eval_structures_static(rafft_ctx *ctx, const void *d_seqs, const void *d_structs, const void *d_offs,
+                                 int32_t n, int64_t total_len, void *d_energy_dcal) {
+  if (!ctx) return RAFFT_ERR_ARG;
+  if (n < 0 || total_len < 0 || (n > 0 && (!d_offs || !d_energy_dcal)) || (total_len > 0 && (!d_seqs || !d_structs))) {
+    ctx->err = "rafft_eval_structures_static: bad argument";
+    return RAFFT_ERR_ARG;
+  }
+  if (total_len > (int64_t)RF_STATIC_EVAL_MAX_LETTERS) {
+    ctx->err = "rafft_eval_structures_static: " + std::to_string(total_len) + " letters exceed the static scratch maximum of " +
+               std::to_string((long long)RF_STATIC_EVAL_MAX_LETTERS) + " (RAFFT_STATIC_EVAL_MAX_LETTERS); split the batch or use rafft_eval_structures";
+    return RAFFT_ERR_ARG;
+  }
+  if (n > (1 << 22)) { ctx->err = "rafft_eval_structures_static: more than 4194304 structures in one call"; return RAFFT_ERR_ARG; }
+  if (n == 0) return RAFFT_OK;
+  CK(cudaSetDevice(ctx->device));
+  unsigned char *scratch = nullptr;
+  if (int rc = static_scratch_of(ctx, &scratch)) return rc;
+  const int wpb = 4;
+  eval_static_kernel<<<(n + wpb - 1) / wpb, wpb * 32, 0, ctx->stream>>>(ctx->d_energy, (const char *)d_seqs, (const char *)d_structs,
+                                                                      (const int64_t *)d_offs, n, total_len, scratch,
+                                                                      (int32_t *)d_energy_dcal);
+  CK(cudaGetLastError());
   CK(cudaStreamSynchronize(ctx->stream));
   return RAFFT_OK;
 }

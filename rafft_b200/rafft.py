@@ -96,6 +96,16 @@ class FoldContext:
         return out[:n]
 
 
+def eval_structures_static(ctx, d_seqs_ptr, d_structs_ptr, d_offs_ptr, n, total_len, d_energy_ptr):
+    """rafft_eval_structures_static: the evaluator on caller-owned DEVICE buffers (raw pointers) with the
+    kernel's scratch in a fixed static device array -- no allocation inside the call.  Not in the
+    reference; see include/rafft_b200.h for the limit (1,048,576 letters) and the sharing rule."""
+    rc = ctx._lib.rafft_eval_structures_static(ctx._h, C.c_void_p(d_seqs_ptr), C.c_void_p(d_structs_ptr),
+                                               C.c_void_p(d_offs_ptr), int(n), int(total_len), C.c_void_p(d_energy_ptr))
+    if rc != N.RAFFT_OK:
+        raise ctx._err(rc)
+
+
 def fold_raw_multi(contexts, seq_bytes, offs, params):
     """One batch folded by several devices from this process (rafft_fold_batch_multi): contiguous
     ranges of the input order, one host thread + stream per device inside the library, one result
