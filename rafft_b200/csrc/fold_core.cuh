@@ -165,6 +165,7 @@ struct Exec {
   RF_FN static int warp() { return threadIdx.x >> 5; }
   RF_FN static int nwarps() { return blockDim.x >> 5; }
   RF_FN static void sync() { __syncthreads(); }
+  RF_FN static void fence_block() { __threadfence_block(); }
   RF_FN static void wsync() { __syncwarp(); }
   RF_FN static int atomic_add(int *p, int v) { return atomicAdd(p, v); }
   RF_FN static unsigned atomic_or(unsigned *p, unsigned v) { return atomicOr(p, v); }
@@ -192,6 +193,18 @@ struct Exec {
   RF_FN static int ffs(unsigned x) { return __ffs((int)x); }
   /* bits [b, b+32) of the 64-bit value hi:lo, 0 <= b < 32 */
   RF_FN static unsigned funnel_r(unsigned lo, unsigned hi, int b) { return __funnelshift_r(lo, hi, b); }
+  /* Sum of v over the block, the same value in every thread, with ONE barrier: per-warp partial sums
+   * go to one of two alternating sets of slots (`wsum`: 16 ints; `turn` counts the calls of a run
+   * of consecutive calls and must be the same in every thread). */
+  RF_FN static int block_sum(int v, int *wsum, int &turn) {
+    v = __reduce_add_sync(0xffffffffu, v);
+    int *w = wsum + ((turn++ & 1) << 3);
+    if ((threadIdx.x & 31) == 0) w[threadIdx.x >> 5] = v;
+    __syncthreads();
+    int t = 0;
+    for (int k = 0; k < (int)(blockDim.x >> 5); k++) t += w[k];
+    return t;
+  }
   /* Block-wide exclusive prefix sum of 0/1 flags (n <= capacity of flag/pref); returns the
    * total.  Must be called by every thread of the block; `wsum` = nwarps+1 ints of shared
    * memory.  Ends with a barrier, so pref[] and the total are visible to all threads. */
@@ -257,6 +270,7 @@ struct Exec {
   static int warp() { return 0; }
   static int nwarps() { return 1; }
   static void sync() {}
+  static void fence_block() {}
   static void wsync() {}
   static int atomic_add(int *p, int v) { int o = *p; *p += v; return o; }
   static unsigned atomic_or(unsigned *p, unsigned v) { unsigned o = *p; *p |= v; return o; }
@@ -281,6 +295,7 @@ struct Exec {
   static unsigned funnel_r(unsigned lo, unsigned hi, int b) {
     return b ? (lo >> b) | (hi << (32 - b)) : lo;
   }
+  static int block_sum(int v, int *, int &turn) { turn++; return v; }
   static int scan_flags(const int *flag, int *pref, int n, int *) {
     int run = 0;
     for (int i = 0; i < n; i++) { pref[i] = run; run += flag[i]; }
@@ -474,6 +489,8 @@ RF_NOINLINE int loop_energy(const EnergyView &ev, int ci, int cj, const int16_t 
  * so the table needs no clean-up pass (the host zeroes it when the generation counter wraps). */
 struct alignas(16) SeenEnt { uint64_t lo, hi; };
 
+struct alignas(8) ActRec { int32_t c, off; }; /* candidates passing for the owning structure, first stem record */
+
 struct Arena {
   uint8_t *code;       /* L_max */
   NodeRec *node;       /* node_cap */
@@ -485,6 +502,8 @@ struct Arena {
   int32_t *nlist;      /* nlist_cap: node lists of stored structures */
   int32_t *ncnt;       /* nlist_cap: candidates of that node passing for the owning structure */
   int32_t *ncoff;      /* nlist_cap: first candidate record of that node (copy of NodeRec::cand_off) */
+  ActRec *act;         /* nlist_cap: per structure (at its nl_off) the regions that HAVE candidates, compacted in
+                          node-list order: what the product enumeration reads (one 32-byte sector = 4 regions) */
   SeenEnt *seen;       /* seen_cap; lo == 0 marks an empty slot (kept clean between runs) */
   unsigned long long *nht;     /* nht_cap: (hash32 << 32) | (node id + 1), 0 = empty */
   NewRec *fresh;       /* new_cap */
@@ -534,7 +553,7 @@ struct SeqState {
   int32_t exp_from;        /* loop records from this id on may still need their expansion */
   int32_t qcnt[16], qbase[16]; /* gather: regions per work list (RF_FAST_LISTS fast lists + generic) */
   int32_t emin, emax, cnt_le;
-  int32_t wsum[12];
+  int32_t wsum[16];
   int64_t seq_off;         /* first letter of the sequence in the batch text */
   unsigned long long cnt[CNT_N];
 };
@@ -610,6 +629,7 @@ RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &
   RF_CARVE(nlist, int32_t, c.nlist_cap);
   RF_CARVE(ncnt, int32_t, c.nlist_cap);
   RF_CARVE(ncoff, int32_t, c.nlist_cap);
+  RF_CARVE(act, ActRec, c.nlist_cap);
   RF_CARVE(fresh, NewRec, c.new_cap);
   RF_CARVE(sel, int32_t, fp.max_stack);
   RF_CARVE(sel_idx, int32_t, fp.max_stack);
@@ -627,7 +647,7 @@ RF_HD size_t arena_carve(Arena &A, char *base, const Caps &c, const FoldParams &
 }
 /* Byte offsets of the arena pieces (computed once on the host, bound per block/warp). */
 struct ArenaOff {
-  uint32_t seen, nht, code, node, pool16, cand, ckid, store, store_db, nlist, ncnt, ncoff, fresh, sel, sel_idx, sel_store, beam, traj_n, traj, todo, todo_id, flag, pref, sel_e;
+  uint32_t seen, nht, code, node, pool16, cand, ckid, store, store_db, nlist, ncnt, ncoff, act, fresh, sel, sel_idx, sel_store, beam, traj_n, traj, todo, todo_id, flag, pref, sel_e;
 };
 RF_HD void arena_bind(Arena &A, char *base, const ArenaOff &o) {
   A.seen = (SeenEnt *)(base + o.seen);
@@ -642,6 +662,7 @@ RF_HD void arena_bind(Arena &A, char *base, const ArenaOff &o) {
   A.nlist = (int32_t *)(base + o.nlist);
   A.ncnt = (int32_t *)(base + o.ncnt);
   A.ncoff = (int32_t *)(base + o.ncoff);
+  A.act = (ActRec *)(base + o.act);
   A.fresh = (NewRec *)(base + o.fresh);
   A.sel = (int32_t *)(base + o.sel);
   A.sel_idx = (int32_t *)(base + o.sel_idx);
@@ -672,6 +693,7 @@ inline void arena_offsets(ArenaOff &o, const Caps &c, const FoldParams &fp) {
   o.nlist = (uint32_t)((char *)A.nlist - base);
   o.ncnt = (uint32_t)((char *)A.ncnt - base);
   o.ncoff = (uint32_t)((char *)A.ncoff - base);
+  o.act = (uint32_t)((char *)A.act - base);
   o.fresh = (uint32_t)((char *)A.fresh - base);
   o.sel = (uint32_t)((char *)A.sel - base);
   o.sel_idx = (uint32_t)((char *)A.sel_idx - base);
@@ -1175,7 +1197,7 @@ struct Fold {
   }
   /* never concurrent with seen_has (block barriers separate the phases); two inserts of one
    * phase carry different fingerprints (the in-chunk table removed the duplicates) */
-  RF_FN void seen_put(uint64_t lo, uint64_t hi) {
+  RF_FN void seen_put(uint64_t lo, uint64_t hi, bool count = true) {
     const uint64_t th = seen_tag(hi), gen = (uint64_t)(uint32_t)this->gen;
     unsigned mask = caps.seen_cap - 1;
     unsigned slot = (unsigned)(lo ^ (hi >> 7)) & mask;
@@ -1184,7 +1206,7 @@ struct Fold {
       if ((cur >> 48) != gen &&
           Exec::atomic_cas64((unsigned long long *)&A.seen[slot].hi, cur, th) == cur) {
         A.seen[slot].lo = lo;
-        Exec::atomic_add(&sh->n_seen, 1);
+        if (count) Exec::atomic_add(&sh->n_seen, 1);
         return;
       }
       slot = (slot + 1) & mask;
@@ -1195,16 +1217,19 @@ struct Fold {
    * itertools.product over the nodes that have candidates, last list varies fastest */
   RF_FN void combo_eval(const StoreRec &S, uint64_t combo, int &e, uint64_t &lo, uint64_t &hi) const {
     e = S.e; lo = S.fp_lo; hi = S.fp_hi;
-    /* four regions at a time: the digits are decoded first, then the four stem records are
-     * fetched together (independent loads in flight instead of one load latency per region) */
-    for (int k0 = S.nl_n - 1; k0 >= 0; k0 -= 4) {
+    /* the regions with candidates, compacted by the first pass of phase_combine (A.act); four at a
+     * time: the digits are decoded first, then the four stem records are fetched together
+     * (independent loads in flight instead of one load latency per region) */
+    const ActRec *act = A.act + S.nl_off;
+    for (int a0 = (int)S.nact - 1; a0 >= 0; a0 -= 4) {
       int at[4];
 #pragma unroll
       for (int j = 0; j < 4; j++) {
-        const int k = k0 - j;
+        const int a = a0 - j;
         at[j] = -1;
-        const uint32_t c = k >= 0 ? (uint32_t)A.ncnt[S.nl_off + k] : 0u;
-        if (c == 0) continue;
+        if (a < 0) continue;
+        const ActRec ar = act[a];
+        const uint32_t c = (uint32_t)ar.c;
         uint32_t dgt = 0;
         if (c != 1) {
           if ((combo >> 32) == 0) { /* the usual case: 32-bit division */
@@ -1214,7 +1239,7 @@ struct Fold {
             dgt = (uint32_t)(combo % c); combo /= c;
           }
         }
-        at[j] = A.ncoff[S.nl_off + k] + (int)dgt;
+        at[j] = ar.off + (int)dgt;
       }
       int de[4];
       uint64_t l[4], h[4];
@@ -1413,6 +1438,7 @@ struct Fold {
      *      of its product, and the reference's work counters (create_childs runs for every
      *      region of every beam member) */
     long long t_exp = 0, t_pos = 0, t_corr = 0, t_scan = 0, t_eval = 0;
+    for (int x = Exec::tid(); x < cs.hcap; x += Exec::stride()) cs.htab[x] = 0; /* in-chunk table of the first chunk */
     RF_PAR_BEGIN(b, beam_n)
       StoreRec &S = A.store[A.beam[b]];
       long long c_pos = 0, c_corr = 0, c_scan = 0, c_eval = 0;
@@ -1426,6 +1452,8 @@ struct Fold {
           A.ncnt[S.nl_off + k] = c;
           A.ncoff[S.nl_off + k] = nd.cand_off;
           if (c > 0) {
+            ActRec ar; ar.c = c; ar.off = nd.cand_off;
+            A.act[S.nl_off + mact] = ar;
             mact++;
             prod = prod > (1ULL << 62) / (uint64_t)c ? (1ULL << 62) : prod * (uint64_t)c;
           }
@@ -1465,60 +1493,63 @@ struct Fold {
     const uint64_t total = cs.mb_pre[nm];
     uint64_t g = 0;
     bool cut = false;
-    while (prm.max_branch > 0 && g < total && !cut && sh->status == ST_OK) {
+    /* Few barriers per chunk (a sequence walks one or two chunks per step, so the chain of
+     * barrier-separated phases IS the latency of this kernel): the running counts live in
+     * registers (every thread derives the same values), evaluation and in-chunk insertion are one
+     * pass, the in-chunk table is cleared for the next chunk while the children are written, and
+     * the `break` position is only looked for when a cut happens. */
+    int n_new_r = 0, nb_branch_r = 0; /* sh->n_new, sh->nb_branch (zeroed above) */
+    bool failed = false;
+    while (prm.max_branch > 0 && g < total && !cut) {
       const int chunk = (int)((total - g) < (uint64_t)CH ? (total - g) : (uint64_t)CH);
-      /* evaluate + look up in `seen` (rafft.py:192-196) */
-      RF_PAR_BEGIN(x, cs.hcap)
-        cs.htab[x] = 0;
-      RF_PAR_END
-      RF_PAR_BEGIN(i, chunk)
+      /* evaluate + look up in `seen` (rafft.py:192-196); the same child reached from two members of
+       * this chunk: only the first one is new -- unseen items enter the in-chunk table at once (an
+       * item's fingerprint is published before its table entry) */
+      for (int i = Exec::tid(); i < chunk; i += Exec::stride()) {
         const uint64_t gi = g + (uint64_t)i;
         const int m = member_of(gi, nm);
         const StoreRec &S = A.store[A.beam[cs.mb_idx[m]]];
         int e_; uint64_t lo_, hi_;
         combo_eval(S, gi - cs.mb_pre[m], e_, lo_, hi_);
         cs.e[i] = e_; cs.lo[i] = lo_; cs.hi[i] = hi_; cs.mem[i] = m;
-        cs.flag[i] = !seen_has(lo_, hi_);
-      RF_PAR_END
-      /* the same child reached from two members of this chunk: only the first one is new */
-      RF_PAR_BEGIN(i, chunk)
-        if (cs.flag[i]) cs.pref[i] = chunk_insert(i);
-      RF_PAR_END
-      RF_PAR_BEGIN(i, chunk)
+        const int unseen = !seen_has(lo_, hi_);
+        cs.flag[i] = unseen;
+        if (unseen) { Exec::fence_block(); cs.pref[i] = chunk_insert(i); }
+      }
+      Exec::sync();
+      for (int i = Exec::tid(); i < chunk; i += Exec::stride())
         if (cs.flag[i]) cs.flag[i] = cs.htab[cs.pref[i]] == i + 1;
-      RF_PAR_END
       const int nnew = Exec::scan_flags(cs.flag, cs.pref, chunk, sh->wsum);
       /* the reference breaks right after the combination that brings nb_branch to
        * max_branch: unseen children number nb0 .. of this chunk are kept up to that one */
-      const int nb0 = sh->nb_branch, base = sh->n_new;
-      const int room = prm.max_branch - nb0; /* > 0 */
+      const int base = n_new_r;
+      const int room = prm.max_branch - nb_branch_r; /* > 0 */
       const int take = nnew < room ? nnew : room;
-      if (base + take > caps.new_cap || 2 * (sh->n_seen + take) + 2 > caps.seen_cap) {
-        RF_SINGLE_BEGIN fail(ST_ERR_CAPACITY); RF_SINGLE_END
-        break;
-      }
-      RF_SINGLE_BEGIN
-        sh->xcut = -1;
-      RF_SINGLE_END
-      RF_PAR_BEGIN(i, chunk)
+      if (base + take > caps.new_cap || 2 * (sh->n_seen + take) + 2 > caps.seen_cap) { failed = true; break; }
+      const bool cutting = nnew >= room;
+      for (int i = Exec::tid(); i < chunk; i += Exec::stride()) {
         if (cs.flag[i] && cs.pref[i] < take) {
           const int m = cs.mem[i];
           NewRec &r = A.fresh[base + cs.pref[i]];
           r.e = cs.e[i]; r.parent_slot = cs.mb_idx[m]; r.combo = g + (uint64_t)i - cs.mb_pre[m];
           r.fp_lo = cs.lo[i]; r.fp_hi = cs.hi[i];
-          seen_put(cs.lo[i], cs.hi[i]);
-          if (nnew >= room && cs.pref[i] == take - 1) sh->xcut = i;
+          seen_put(cs.lo[i], cs.hi[i], false); /* counted once per chunk below: no atomic per child */
+          if (cutting && cs.pref[i] == take - 1) sh->xcut = i;
         }
-      RF_PAR_END
-      const int xcut = sh->xcut;
-      const int upto = xcut >= 0 ? xcut + 1 : chunk;
-      RF_SINGLE_BEGIN
-        sh->n_new += take;
-        sh->nb_branch += take;
-      RF_SINGLE_END
+      }
+      if (Exec::tid() == 0) sh->n_seen += take; /* nobody reads it before the barrier */
+      for (int x = Exec::tid(); x < cs.hcap; x += Exec::stride()) cs.htab[x] = 0; /* for the next chunk */
+      Exec::sync(); /* the children are in `seen` before the next chunk looks it up */
+      const int upto = cutting ? sh->xcut + 1 : chunk;
+      n_new_r += take;
+      nb_branch_r += take;
       g += (uint64_t)upto;
-      cut = xcut >= 0;
+      cut = cutting;
     }
+    RF_SINGLE_BEGIN
+      sh->n_new = n_new_r; sh->nb_branch = nb_branch_r;
+      if (failed) fail(ST_ERR_CAPACITY);
+    RF_SINGLE_END
     if (sh->status != ST_OK) { finish_fold(); return; }
     /* which members were exhausted, where the enumeration stopped, and the reference's counters:
      * an exhausted member met before the stop is walked again in full by the reference (all its
@@ -1619,21 +1650,15 @@ struct Fold {
       }
       Exec::sync();
       long long blo = sh->emin, bhi = sh->emax; /* smallest T with count(e <= T) >= keep */
-      while (blo < bhi) {
+      int turn = 0;
+      while (blo < bhi) { /* one barrier per bisection step */
         const long long mid = (blo + bhi) >> 1; /* floor */
-        RF_SINGLE_BEGIN
-          sh->cnt_le = 0;
-        RF_SINGLE_END
         int c = 0;
         for (int i = Exec::tid(); i < total; i += Exec::stride()) c += RF_ENTRY_E(i) <= mid;
-        if (c) Exec::atomic_add(&sh->cnt_le, c);
-        Exec::sync();
-        if (sh->cnt_le >= keep) bhi = mid; else blo = mid + 1;
+        if (Exec::block_sum(c, sh->wsum, turn) >= keep) bhi = mid; else blo = mid + 1;
       }
       const int T_e = (int)blo;
-      RF_SINGLE_BEGIN
-        sh->cnt_le = 0;
-      RF_SINGLE_END
+      int n_below;
       {
         int c = 0;
         for (int i = Exec::tid(); i < total; i += Exec::stride()) {
@@ -1641,10 +1666,9 @@ struct Fold {
           c += e < T_e;
           A.flag[i] = e == T_e;
         }
-        if (c) Exec::atomic_add(&sh->cnt_le, c);
+        n_below = Exec::block_sum(c, sh->wsum, turn);
       }
-      Exec::sync();
-      const int need_eq = keep - sh->cnt_le; /* >= 1 */
+      const int need_eq = keep - n_below; /* >= 1 */
       Exec::scan_flags(A.flag, A.pref, total, sh->wsum);
       RF_PAR_BEGIN(i, total)
         int e = RF_ENTRY_E(i);

@@ -78,7 +78,8 @@ struct WaveCtx {
   FastCfg fast;
   BigCfg big;
   LoopCtl *ctl;
-  int32_t *alist;     /* two lists of acap wave slots: the sequences still folding */
+  int32_t *alist;     /* two lists of acap wave slots: the sequences still folding; behind them acap flags
+                         (slot still folding after this step?) written by k_materialise, read by k_advance */
   int32_t acap;
   int32_t sel_smem;   /* bytes of shared memory for the energies under selection (0: global) */
   int32_t fuse;       /* 1: select + materialise + the next step's gather run as one kernel (k_beam) */
@@ -206,12 +207,12 @@ __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_select(RF_WAVE_PARAM) 
 
 __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_materialise(RF_WAVE_PARAM) {
   __shared__ SeqState sh;
-  int32_t *next_list = c.alist + (size_t)(c.ctl->parity ^ 1) * (size_t)c.acap;
+  int32_t *aflag = c.alist + 2 * (size_t)c.acap;
   RF_FOR_ACTIVE(3)
     Fold f(c.E, c.prm, c.caps);
-    if (!BlockBind::load(c, f, &sh, j, true)) continue;
+    if (!BlockBind::load(c, f, &sh, j, true)) { if (threadIdx.x == 0) aflag[j] = 0; continue; }
     f.phase_materialise();
-    if (threadIdx.x == 0 && sh.active) next_list[atomicAdd(&c.ctl->n_next, 1)] = j;
+    if (threadIdx.x == 0) aflag[j] = sh.active; /* k_advance builds the next list from these */
     BlockBind::store(c, &sh, j);
   RF_END_ACTIVE
 }
@@ -221,36 +222,69 @@ __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_materialise(RF_WAVE_PA
 __global__ void __launch_bounds__(RF_BLOCK_THREADS_MAX) k_beam(RF_WAVE_PARAM) {
   __shared__ SeqState sh;
   extern __shared__ __align__(16) char select_smem[];
-  int32_t *next_list = c.alist + (size_t)(c.ctl->parity ^ 1) * (size_t)c.acap;
+  int32_t *aflag = c.alist + 2 * (size_t)c.acap;
   RF_FOR_ACTIVE(2)
     Fold f(c.E, c.prm, c.caps);
-    if (!BlockBind::load(c, f, &sh, j, true)) continue;
+    if (!BlockBind::load(c, f, &sh, j, true)) { if (threadIdx.x == 0) aflag[j] = 0; continue; }
     if (c.sel_smem) f.A.sel_e = (int32_t *)select_smem;
     f.phase_select();
     __syncthreads();
     f.phase_materialise();
     __syncthreads();
     f.phase_gather();
-    if (threadIdx.x == 0 && sh.active) next_list[atomicAdd(&c.ctl->n_next, 1)] = j;
+    if (threadIdx.x == 0) aflag[j] = sh.active;
     BlockBind::store(c, &sh, j);
   RF_END_ACTIVE
 }
 
-/* end of a folding iteration: the next active list becomes the current one, the work lists and
- * cursors are cleared, and the loop condition is set (graph WHILE node) / published to the host
- * (stream mode) */
-__global__ void k_advance(LoopCtl *ctl, int32_t *h_prog, cudaGraphConditionalHandle handle, int use_handle, int fuse) {
-  const int t = threadIdx.x;
-  if (!fuse) clear_work_lists(ctl);
+/* end of a folding iteration (one block of RF_ADVANCE_THREADS threads): the sequences of the current
+ * active list that are still folding are compacted IN ORDER into the other list -- the initial order
+ * is longest first, and keeping it means the persistent kernels of every later step still start their
+ * heaviest sequences first (an atomic append would leave them in completion order: heaviest last) --
+ * then the work lists and cursors are cleared and the loop condition is set (graph WHILE node) /
+ * published to the host (stream mode) */
+#define RF_ADVANCE_THREADS 1024
+__global__ void __launch_bounds__(RF_ADVANCE_THREADS) k_advance(RF_WAVE_PARAM, cudaGraphConditionalHandle handle, int use_handle) {
+  __shared__ int s_warp[RF_ADVANCE_THREADS / 32];
+  LoopCtl *ctl = c.ctl;
+  const int t = threadIdx.x, T = blockDim.x;
+  const int n_cur = ctl->n_cur, parity = ctl->parity;
+  const int32_t *cur = c.alist + (size_t)parity * (size_t)c.acap;
+  int32_t *nxt = c.alist + (size_t)(parity ^ 1) * (size_t)c.acap;
+  const int per = (n_cur + T - 1) / T;
+  const int lo = min(n_cur, t * per), hi = min(n_cur, lo + per);
+  const int32_t *aflag = c.alist + 2 * (size_t)c.acap; /* dense, and cur[] is ascending: sequential reads */
+  int cnt = 0;
+  for (int k = lo; k < hi; k++) cnt += aflag[cur[k]] != 0;
+  int inc = cnt;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, inc, d);
+    if ((t & 31) >= d) inc += v;
+  }
+  if ((t & 31) == 31) s_warp[t >> 5] = inc;
+  __syncthreads();
+  int base = 0, total = 0;
+  for (int w = 0; w < (T >> 5); w++) {
+    const int v = s_warp[w];
+    if (w < (t >> 5)) base += v;
+    total += v;
+  }
+  int at = base + inc - cnt;
+  for (int k = lo; k < hi; k++) {
+    const int j = cur[k];
+    if (aflag[j]) nxt[at++] = j;
+  }
+  if (!c.fuse) clear_work_lists(ctl);
   if (t < 4) ctl->work[t] = 0;
   if (t == 0) {
-    const int n = ctl->n_next;
-    ctl->n_cur = n; ctl->n_next = 0; ctl->parity ^= 1;
+    const int n = total;
+    ctl->n_cur = n; ctl->n_next = 0; ctl->parity = parity ^ 1;
     const int it = ++ctl->iters;
     if (use_handle) cudaGraphSetConditional(handle, n > 0 ? 1u : 0u);
-    if (n == 0) h_prog[1] = 1;
+    if (n == 0) c.h_prog[1] = 1;
     __threadfence_system();
-    h_prog[0] = it;
+    c.h_prog[0] = it;
   }
 }
 
@@ -1100,11 +1134,8 @@ static void emit_iteration(Emit &E, WavePlan &P, cudaGraphConditionalHandle hand
   if (wc.fuse) E.kernel((const void *)k_beam, dim3(P.g_mat), dim3(P.T_mat), (size_t)wc.sel_smem, a_wc);
   else E.kernel((const void *)k_materialise, dim3(P.g_mat), dim3(P.T_mat), 0, a_wc);
   mark();
-  LoopCtl *ctl = wc.ctl;
-  int32_t *hp = wc.h_prog;
-  int fuse = wc.fuse;
-  void *a_adv[] = {&ctl, &hp, &handle, &use_handle, &fuse};
-  E.kernel((const void *)k_advance, dim3(1), dim3(32), 0, a_adv);
+  void *a_adv[] = {&wc, &handle, &use_handle};
+  E.kernel((const void *)k_advance, dim3(1), dim3(RF_ADVANCE_THREADS), 0, a_adv);
   mark();
 }
 
@@ -1308,7 +1339,7 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
     if (int rc = dev_reserve_s(ln.err, ln.ftasks, sizeof(int32_t) * 2 * RF_FAST_LISTS * (size_t)(fcap + 1))) return rc;
     if (int rc = dev_reserve_s(ln.err, ln.scratch, (size_t)qcap * (size_t)caps.wscratch_bytes)) return rc;
     if (int rc = dev_reserve_s(ln.err, ln.btasks, sizeof(int32_t) * 2 * (size_t)(bcap + 1))) return rc;
-    if (int rc = dev_reserve_s(ln.err, ln.alist, sizeof(int32_t) * 2 * (size_t)wave)) return rc;
+    if (int rc = dev_reserve_s(ln.err, ln.alist, sizeof(int32_t) * 3 * (size_t)wave)) return rc;
     WaveCtx &wc = P.wc;
     memset(&wc, 0, sizeof wc);
     wc.E = ctx->d_energy; wc.prm = F; wc.caps = caps;
