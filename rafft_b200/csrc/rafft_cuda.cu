@@ -1229,13 +1229,8 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
   };
   WavePlan P;
   P.T = Tb;
-  /* measured on B200 (tools/threads_sweep.sh): the product enumeration wants 4 warps per sequence
-   * (more look-ups in flight), selection and materialisation 2 warps up to -ms 100 and 4 beyond */
-  const int T_ms = J.params->max_stack > 100 && Tb == 64 ? 128 : Tb;
+  /* block sizes of the beam kernels: set per round below, once the wave size is known */
   P.T_gather = threads_of("RAFFT_GATHER_THREADS", Tb);
-  P.T_combine = threads_of("RAFFT_COMBINE_THREADS", Tb == 64 ? 128 : Tb);
-  P.T_select = threads_of("RAFFT_SELECT_THREADS", T_ms);
-  P.T_mat = threads_of("RAFFT_MATERIALISE_THREADS", T_ms);
   P.T_finish = threads_of("RAFFT_FINISH_THREADS", RF_BLOCK_THREADS_MAX);
 
   /* index part of the output */
@@ -1333,6 +1328,18 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
         ln.arena_clean = need;
       }
       ln.arena_dirty = true; /* until this fold has run to its end */
+    }
+    {
+      /* measured on B200 (tools/threads_sweep.sh, tools/probe/r2_small_threads.sh): with many sequences per
+       * resident block the product enumeration wants 4 warps per sequence (more look-ups in flight),
+       * selection and materialisation 2 warps up to -ms 100 and 4 beyond; when a wave is so small that a
+       * persistent block gets about ONE sequence (a shard of a strong-scaling run), the kernel's time is
+       * the time of its heaviest sequence and wider blocks shorten it (-5 % at 1,250 sequences, cfg 2 / 3) */
+      const bool small = wave <= (int64_t)ctx->sm_count * 10 && Tb == 64;
+      const int T_ms = small ? (J.params->max_stack > 100 ? 256 : 128) : (J.params->max_stack > 100 && Tb == 64 ? 128 : Tb);
+      P.T_combine = threads_of("RAFFT_COMBINE_THREADS", small ? 256 : (Tb == 64 ? 128 : Tb));
+      P.T_select = threads_of("RAFFT_SELECT_THREADS", T_ms);
+      P.T_mat = threads_of("RAFFT_MATERIALISE_THREADS", T_ms);
     }
     if (int rc = dev_reserve_s(ln.err, ln.states, sizeof(SeqState) * (size_t)wave)) return rc;
     if (int rc = dev_reserve_s(ln.err, ln.tasks, sizeof(int32_t) * 2 * (size_t)qcap)) return rc;
