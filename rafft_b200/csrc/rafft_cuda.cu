@@ -325,6 +325,7 @@ template <int K>
 __device__ __forceinline__ void fast_class(const WaveCtx &c, int cls, char *ws, int *s_base) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int nt = min(c.Q.n_fast[cls], c.Q.fast_cap);
+  if (nt == 0) return; /* an empty class costs nothing (late steps: most are; the count is the same for every thread) */
   const int32_t *list = c.Q.fast_task + 2 * (size_t)cls * (size_t)c.Q.fast_cap;
   for (;;) {
     __syncthreads();
