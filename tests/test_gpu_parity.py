@@ -396,3 +396,18 @@ def test_parameter_file_context(ctx, tmp_path):
     other, _ = gpu_steps(c3, seqs, nb_mode=100, max_stack=10)
     assert other != want
     c3.close()
+
+
+def test_cli_devices_flag(tmp_path, oracle):
+    "bin/rafft --devices all: one process folds the FASTA records on every GPU of the box, output in input order"
+    from rafft_b200.utils import energy_from_dcal
+    seqs = [splitmix_seq(800 + k, L) for k, L in enumerate((60, 45, 120, 33, 90, 75))]
+    fa = tmp_path / "in.fa"
+    fa.write_text("".join(">s%d\n%s\n" % (k, s) for k, s in enumerate(seqs)))
+    want = [oracle.fold(s, 50, 3, 1000)[-1] for s in seqs]
+    lines = [l for s, beam in zip(seqs, want) for l in [s] + ["%s %6.1f" % (db, energy_from_dcal(e)) for db, e in beam]]
+    for dev in ("all", "0"):
+        out = subprocess.run([sys.executable, os.path.join(ROOT, "bin", "rafft"), "-sf", str(fa), "--batch", "-n", "50",
+                              "-ms", "3", "--devices", dev], capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0, out.stderr
+        assert out.stdout.splitlines() == lines, dev
