@@ -278,11 +278,16 @@ __global__ void __launch_bounds__(RF_ADVANCE_THREADS) k_advance(RF_WAVE_PARAM, c
   if (!c.fuse) clear_work_lists(ctl);
   if (t < 4) ctl->work[t] = 0;
   if (t == 0) {
-    const int n = total;
-    ctl->n_cur = n; ctl->n_next = 0; ctl->parity = parity ^ 1;
+    int n = total;
     const int it = ++ctl->iters;
+    /* no fold needs more iterations than folding steps fit its trajectory plus the rounds a full work list
+     * can defer: beyond that the loop is stopped (the device-side WHILE has no host to give up for it) and
+     * the host reports the call as failed */
+    const bool runaway = n > 0 && it >= 8 * c.caps.step_cap + 4096;
+    if (runaway) n = 0;
+    ctl->n_cur = n; ctl->n_next = 0; ctl->parity = parity ^ 1;
     if (use_handle) cudaGraphSetConditional(handle, n > 0 ? 1u : 0u);
-    if (n == 0) c.h_prog[1] = 1;
+    if (n == 0) c.h_prog[1] = runaway ? 2 : 1;
     __threadfence_system();
     c.h_prog[0] = it;
   }
@@ -1504,6 +1509,7 @@ static int lane_fold(FoldJob &J, int k) {  /* first half: the fold itself, up to
       LCK(cudaMemcpyAsync(ln.h_small + 32, &ctl->iters, sizeof(int32_t), cudaMemcpyDeviceToHost, ln.stream));
       LCK(cudaStreamSynchronize(ln.stream));
       const int iters = *(const int32_t *)(ln.h_small + 32);
+      if (((volatile int32_t *)h_prog)[1] == 2) { ln.err = "no progress: the folding loop was stopped after " + std::to_string(iters) + " iterations"; return RAFFT_ERR_CUDA; }
       T.iters += iters;
       T.launches += 2 + (int64_t)iters * per_iter;
       T.d2h += 4;
