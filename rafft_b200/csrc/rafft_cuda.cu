@@ -2,9 +2,10 @@
  * rafft_cuda.cu -- the C-ABI library (include/rafft_b200.h) over the sm_100a kernels.
  *
  * Kernels in this file:
- *   k_ctl_reset / k_init / k_gather / k_expand_fast / k_expand<1..5> / k_combine / k_select /
- *   k_materialise / k_advance / k_finish
- *                  the level-synchronous phase kernels of the fold (fold_core.cuh, expand_fast.cuh).
+ *   k_ctl_reset / k_init / k_gather / k_expand_fast / k_expand_big / k_expand<1..5> / k_combine /
+ *   k_select / k_materialise / (k_beam) / k_advance / k_finish
+ *                  the level-synchronous phase kernels of the fold (fold_core.cuh, expand_fast.cuh,
+ *                  expand_big.cuh).
  *                  One folding iteration of every sequence of a wave is the chain
  *                  gather -> expand -> combine -> select -> materialise -> advance; the chain is the
  *                  body of a CUDA-graph WHILE node whose condition k_advance sets on the device, so a
@@ -14,6 +15,8 @@
  *   scan_kernel    exclusive scans that turn per-sequence counts into the ordered layout
  *   pack_kernel    gathers the bump-allocated results into input order
  *   eval_kernel    whole-structure loop-decomposition energies (rafft_eval_structures)
+ *   eval_static_kernel  the same with its scratch in a file-scope device array (rafft_eval_structures_static:
+ *                  no allocation inside the call)
  *   int_peak_kernel  IADD3/LOP3 issue-rate microbenchmark (rafft_int_peak: the roofline denominator)
  *
  * There is no CPU fallback: every entry point fails with RAFFT_ERR_CUDA when no device is

@@ -77,3 +77,18 @@ def test_emu_long_region_ranks_by_selection(emu, oracle):
     for rev in (0, 1):
         rc, steps, _, _ = emu(seq, reverse=rev, nb_mode=60, max_stack=3)
         assert rc == 0 and steps == want
+
+
+def test_emu_cut_positions_across_small_chunks(emu, oracle):
+    """the product enumeration in chunks of 4-8 combinations with the max_branch cut falling on every position
+    (first / last item of a chunk, chunk boundaries, later members trying their first combination only):
+    the running counts kept in registers and the in-chunk duplicate table of phase_combine"""
+    seqs = [splitmix_seq(1200 + k, L) for k, L in enumerate((48, 70, 95))]
+    for seq in seqs:
+        for max_stack in (2, 5, 8):
+            for max_branch in (1, 2, 3, 4, 5, 7, 8, 9, 13, 16, 17, 31):
+                kw = dict(nb_mode=40, max_stack=max_stack, max_branch=max_branch)
+                rc, steps, cnt, _ = emu(seq, nthreads=1, **kw)
+                want, wcnt = oracle.fold(seq, counters=True, **kw)
+                assert rc == 0 and steps == want, (len(seq), kw)
+                assert cnt[:5] == wcnt[:5] and cnt[8:10] == wcnt[8:10], (len(seq), kw)
